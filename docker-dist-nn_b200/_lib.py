@@ -1,0 +1,90 @@
+"""ctypes binding of libddnn.so -- the only way Python reaches the kernels.
+
+There is no CPU fallback: if the shared object is missing (and cannot be built because
+nvcc is absent) importing this module raises, and every wrapper raises on a non-zero
+status.  ``SYMBOLS`` lists every entry point ``include/ddnn.h`` declares.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libddnn.so"
+
+# status codes / enums (include/ddnn.h)
+OK, ERR_DIM, ERR_ACTIVATION, ERR_CUDA, ERR_ARG, ERR_WORKSPACE, ERR_UNSUPPORTED = range(7)
+ACT_LINEAR, ACT_RELU, ACT_SIGMOID, ACT_SOFTMAX = range(4)
+F32, BF16 = 0, 1
+ENGINE_AUTO, ENGINE_SIMT, ENGINE_TCGEN05 = 0, 1, 2
+
+_vp, _i64, _i32, _f32, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_size_t
+
+SYMBOLS = {
+    "ddnn_version": (C.c_int, []),
+    "ddnn_last_error": (C.c_char_p, []),
+    "ddnn_activation_from_name": (C.c_int, [C.c_char_p]),
+    "ddnn_set_engine": (C.c_int, [_i32]),
+    "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
+    "ddnn_softmax_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp]),
+    "ddnn_activate": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp]),
+    "ddnn_softmax_ce": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _i32, _i32, _vp]),
+    "ddnn_dense_backward_dx": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _vp]),
+    "ddnn_dense_backward_dw_sgd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
+                                             _i32, _vp, _sz, _vp]),
+    "ddnn_dw_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
+    "ddnn_cast_f32_to_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
+    "ddnn_cast_bf16_to_f32": (C.c_int, [_vp, _vp, _i64, _vp]),
+    "ddnn_launch_count": (_i64, []),
+}
+
+
+class DdnnError(RuntimeError):
+    def __init__(self, status: int, text: str):
+        super().__init__(f"libddnn status {status}: {text}")
+        self.status = status
+        self.text = text
+
+
+def _load() -> C.CDLL:
+    if not LIB_PATH.exists():
+        try:
+            from .build import build
+            build()
+        except Exception as e:  # noqa: BLE001
+            raise RuntimeError(
+                f"libddnn.so is missing at {LIB_PATH} and could not be built ({e}). "
+                "There is no CPU fallback; run `python docker-dist-nn_b200/build.py`.") from e
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the header and the library disagree
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+
+def last_error() -> str:
+    return (lib.ddnn_last_error() or b"").decode("utf-8", "replace")
+
+
+def check(status: int) -> None:
+    if status != OK:
+        raise DdnnError(status, last_error())
+
+
+def activation_id(name) -> int:
+    """grpc_node.py:62-73 string -> enum; unknown strings (and None) are linear."""
+    if name is None:
+        return ACT_LINEAR
+    return lib.ddnn_activation_from_name(str(name).encode())
+
+
+def launch_count() -> int:
+    return int(lib.ddnn_launch_count())
+
+
+def set_engine(engine: int) -> None:
+    check(lib.ddnn_set_engine(engine))

@@ -1,0 +1,253 @@
+// extern "C" boundary of libddnn.so (see include/ddnn.h).  Validates arguments, picks the
+// engine (tcgen05 GEMMs for aligned bf16 layers, SIMT kernels otherwise) and launches.
+#include <cstring>
+#include <string>
+
+#include "ddnn_internal.h"
+
+namespace ddnn {
+
+static thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+static std::atomic<int> g_engine{DDNN_ENGINE_AUTO};
+
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+static int check_dims(const char* fn, int64_t B, int64_t K, int64_t N) {
+  if (B < 0 || K <= 0 || N <= 0 || B > INT32_MAX || K > INT32_MAX || N > INT32_MAX) {
+    set_error("%s: bad dimensions B=%lld K=%lld N=%lld", fn, (long long)B, (long long)K, (long long)N);
+    return DDNN_ERR_DIM;
+  }
+  return DDNN_OK;
+}
+
+// tcgen05 path: bf16 operands, 16-byte aligned rows (widths % 8) and pointers.
+static bool use_umma(int dtype, int64_t B, int64_t K, int64_t N, std::initializer_list<const void*> ptrs) {
+  const int e = g_engine.load();
+  if (e == DDNN_ENGINE_SIMT || dtype != DDNN_BF16) return false;
+  if (!umma_shape_ok(B, K, N)) return false;
+  for (const void* p : ptrs)
+    if (p && !aligned16(p)) return false;
+  if (e == DDNN_ENGINE_TCGEN05) return true;
+  // AUTO: tiny layers are launch-latency bound either way; keep them on the SIMT kernels
+  return K >= 64 && N >= 64;
+}
+
+}  // namespace ddnn
+
+using namespace ddnn;
+
+extern "C" {
+
+int ddnn_version(void) { return 100; }
+
+const char* ddnn_last_error(void) { return g_err.c_str(); }
+
+int ddnn_activation_from_name(const char* name) {
+  if (!name) return DDNN_ACT_LINEAR;
+  if (!strcmp(name, "relu")) return DDNN_ACT_RELU;
+  if (!strcmp(name, "sigmoid")) return DDNN_ACT_SIGMOID;
+  if (!strcmp(name, "softmax")) return DDNN_ACT_SOFTMAX;
+  return DDNN_ACT_LINEAR;  // grpc_node.py:72-73: everything else is the identity
+}
+
+int ddnn_set_engine(int engine) {
+  if (engine < DDNN_ENGINE_AUTO || engine > DDNN_ENGINE_TCGEN05) {
+    set_error("ddnn_set_engine: bad engine %d", engine);
+    return DDNN_ERR_ARG;
+  }
+  g_engine.store(engine);
+  return DDNN_OK;
+}
+
+int64_t ddnn_launch_count(void) { return (int64_t)g_launches.load(); }
+
+int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K, int64_t N,
+                       int act, int dtype, int out_dtype, void* stream) {
+  int rc = check_dims("ddnn_dense_forward", B, K, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!X || !W || !bias || !A) {
+    set_error("ddnn_dense_forward: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (act < DDNN_ACT_LINEAR || act > DDNN_ACT_SOFTMAX) {
+    set_error("ddnn_dense_forward: bad activation %d", act);
+    return DDNN_ERR_ACTIVATION;
+  }
+  if (act == DDNN_ACT_SOFTMAX && out_dtype != DDNN_F32) {
+    set_error("ddnn_dense_forward: softmax output must be fp32");
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int gemm_act = act == DDNN_ACT_SOFTMAX ? DDNN_ACT_LINEAR : act;
+  if (use_umma(dtype, B, K, N, {X, W, A}))
+    rc = umma_forward((const bf16*)X, (const bf16*)W, bias, A, B, K, N, gemm_act, out_dtype, st);
+  else
+    rc = simt_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
+  if (rc) return rc;
+  if (act == DDNN_ACT_SOFTMAX) rc = softmax_rows((const float*)A, (float*)A, B, N, st);
+  return rc;
+}
+
+int ddnn_softmax_rows(const float* Z, float* P, int64_t B, int64_t N, void* stream) {
+  int rc = check_dims("ddnn_softmax_rows", B, 1, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!Z || !P) {
+    set_error("ddnn_softmax_rows: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  return softmax_rows(Z, P, B, N, (cudaStream_t)stream);
+}
+
+int ddnn_activate(const float* V, float* out, int64_t B, int64_t N, int act, void* stream) {
+  int rc = check_dims("ddnn_activate", B, 1, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!V || !out) {
+    set_error("ddnn_activate: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (act < DDNN_ACT_LINEAR || act > DDNN_ACT_SOFTMAX) {
+    set_error("ddnn_activate: bad activation %d", act);
+    return DDNN_ERR_ACTIVATION;
+  }
+  return activate(V, out, B, N, act, (cudaStream_t)stream);
+}
+
+int ddnn_softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ, float* row_loss, float* loss,
+                    int64_t B, int64_t N, float inv_denom, int dz_dtype, int accumulate, void* stream) {
+  int rc = check_dims("ddnn_softmax_ce", B, 1, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!Z || !labels) {
+    set_error("ddnn_softmax_ce: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (P == Z) {
+    set_error("ddnn_softmax_ce: P must not alias Z");
+    return DDNN_ERR_ARG;
+  }
+  return softmax_ce(Z, labels, P, dZ, row_loss, loss, B, N, inv_denom, dz_dtype, accumulate, (cudaStream_t)stream);
+}
+
+int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev, int64_t B, int64_t K,
+                           int64_t N, int act_prev, int dtype, void* stream) {
+  int rc = check_dims("ddnn_dense_backward_dx", B, K, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!dZ || !W || !dZprev) {
+    set_error("ddnn_dense_backward_dx: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (act_prev == DDNN_ACT_SOFTMAX) {
+    set_error("ddnn_dense_backward_dx: hidden softmax layers are not supported (row Jacobian)");
+    return DDNN_ERR_ACTIVATION;
+  }
+  if (act_prev < DDNN_ACT_LINEAR || act_prev > DDNN_ACT_SOFTMAX) {
+    set_error("ddnn_dense_backward_dx: bad activation %d", act_prev);
+    return DDNN_ERR_ACTIVATION;
+  }
+  if (act_prev != DDNN_ACT_LINEAR && !Aprev) {
+    set_error("ddnn_dense_backward_dx: Aprev is required for activation %d", act_prev);
+    return DDNN_ERR_ARG;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  if (use_umma(dtype, B, K, N, {dZ, W, Aprev, dZprev}))
+    return umma_dx((const bf16*)dZ, (const bf16*)W, (const bf16*)Aprev, (bf16*)dZprev, B, K, N, act_prev, st);
+  return simt_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
+}
+
+static size_t np_of(int64_t N) { return (size_t)((N + 3) & ~(int64_t)3); }
+
+size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
+  if (B <= 0 || K <= 0 || N <= 0) return 0;
+  const size_t np = np_of(N);
+  // SIMT plan: dW partials [splits][K][np] + db partials [splits][np]
+  const size_t s1 = (size_t)simt_dw_splits(B, K, N);
+  size_t simt = s1 * ((size_t)K + 1) * np * sizeof(float);
+  size_t umma = 0;
+  if (dtype == DDNN_BF16 && umma_shape_ok(B, K, N)) {
+    const size_t s2 = (size_t)umma_dw_splits(B, K, N);
+    umma = (s2 > 1 ? s2 * (size_t)K * np : 0) * sizeof(float) + (size_t)colsum_splits(B, N) * np * sizeof(float);
+  }
+  size_t need = simt > umma ? simt : umma;
+  return (need + 255) & ~(size_t)255;
+}
+
+int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, void* W_shadow, float* bias,
+                               float* dW_out, float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N,
+                               int dtype, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = check_dims("ddnn_dense_backward_dw_sgd", B, K, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!X || !dZ) {
+    set_error("ddnn_dense_backward_dw_sgd: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (apply ? (!W_master || !bias) : (!dW_out || !db_out)) {
+    set_error("ddnn_dense_backward_dw_sgd: missing %s", apply ? "W_master/bias" : "dW_out/db_out");
+    return DDNN_ERR_ARG;
+  }
+  const size_t need = ddnn_dw_workspace_bytes(B, K, N, dtype);
+  if (!workspace || workspace_bytes < need || !aligned16(workspace)) {
+    set_error("ddnn_dense_backward_dw_sgd: workspace %zu bytes < %zu required (or misaligned)", workspace_bytes, need);
+    return DDNN_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t np = np_of(N);
+  float* ws = (float*)workspace;
+  if (use_umma(dtype, B, K, N, {X, dZ, W_master, W_shadow, dW_out})) {
+    const int splits = umma_dw_splits(B, K, N);
+    float* dw_part = splits > 1 ? ws : nullptr;
+    float* db_part = ws + (splits > 1 ? (size_t)splits * K * np : 0);
+    const int cs = colsum_splits(B, N);
+    rc = umma_dw((const bf16*)X, (const bf16*)dZ, dw_part, splits, W_master, (bf16*)W_shadow, dW_out, lr, apply, B, K,
+                 N, st);
+    if (rc) return rc;
+    rc = colsum_partials(dZ, db_part, cs, B, N, dtype, st);
+    if (rc) return rc;
+    if (splits > 1 && cs != splits) {
+      // two reductions with different split counts: weights first, then the bias row
+      rc = reduce_dw(dw_part, nullptr, splits, K, N, W_master, W_shadow, nullptr, dW_out, nullptr, lr, apply, st);
+      if (rc) return rc;
+      return reduce_dw(nullptr, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+    }
+    return reduce_dw(dw_part, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+  }
+  const int splits = simt_dw_splits(B, K, N);
+  float* dw_part = ws;
+  float* db_part = ws + (size_t)splits * K * np;
+  rc = simt_dw_partials(X, dZ, dw_part, db_part, splits, B, K, N, dtype, st);
+  if (rc) return rc;
+  return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+}
+
+int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream) {
+  if (n <= 0) return DDNN_OK;
+  if (!in || !out || !aligned16(in) || (reinterpret_cast<uintptr_t>(out) & 7u)) {
+    set_error("ddnn_cast_f32_to_bf16: null or misaligned pointer");
+    return DDNN_ERR_ARG;
+  }
+  return cast_f32_bf16(in, (bf16*)out, n, (cudaStream_t)stream);
+}
+int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream) {
+  if (n <= 0) return DDNN_OK;
+  if (!in || !out || !aligned16(out) || (reinterpret_cast<uintptr_t>(in) & 7u)) {
+    set_error("ddnn_cast_bf16_to_f32: null or misaligned pointer");
+    return DDNN_ERR_ARG;
+  }
+  return cast_bf16_f32((const bf16*)in, out, n, (cudaStream_t)stream);
+}
+
+}  // extern "C"

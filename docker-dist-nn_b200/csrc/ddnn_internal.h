@@ -1,0 +1,48 @@
+// Internal launch interface between ddnn_api.cu and the kernel translation units.
+#pragma once
+#include "ddnn_common.cuh"
+
+namespace ddnn {
+
+// ---- SIMT fp32-accumulate GEMMs (ddnn_simt.cu) ---------------------------------------
+int simt_forward(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K,
+                 int64_t N, int act, int dtype, int out_dtype, cudaStream_t st);
+int simt_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev, int64_t B, int64_t K,
+            int64_t N, int act_prev, int dtype, cudaStream_t st);
+// Writes split-K partials: dw_part[z][K][Np] and db_part[z][Np]  (Np = N rounded up to 4).
+int simt_dw_partials(const void* X, const void* dZ, float* dw_part, float* db_part, int splits,
+                     int64_t B, int64_t K, int64_t N, int dtype, cudaStream_t st);
+int simt_dw_splits(int64_t B, int64_t K, int64_t N);
+
+// ---- split-K reduction + dW epilogue (ddnn_reduce.cu) --------------------------------
+// Sums partials in z order, then SGD (apply) or fp32 store.
+int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K, int64_t N,
+              float* W_master, void* W_shadow, float* bias, float* dW_out, float* db_out, float lr,
+              int apply, cudaStream_t st);
+// db partials from dZ alone (used by the tcgen05 path): db_part[z][Np]
+int colsum_partials(const void* dZ, float* db_part, int splits, int64_t B, int64_t N, int dtype,
+                    cudaStream_t st);
+int colsum_splits(int64_t B, int64_t N);
+
+// ---- softmax family (ddnn_softmax.cu) -------------------------------------------------
+int softmax_rows(const float* Z, float* P, int64_t B, int64_t N, cudaStream_t st);
+int softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ, float* row_loss,
+               float* loss, int64_t B, int64_t N, float inv_denom, int dz_dtype, int accumulate,
+               cudaStream_t st);
+int activate(const float* V, float* out, int64_t B, int64_t N, int act, cudaStream_t st);
+int cast_f32_bf16(const float* in, bf16* out, int64_t n, cudaStream_t st);
+int cast_bf16_f32(const bf16* in, float* out, int64_t n, cudaStream_t st);
+
+// ---- tcgen05 / TMA / TMEM GEMMs (ddnn_umma.cu) ----------------------------------------
+bool umma_shape_ok(int64_t B, int64_t K, int64_t N);
+int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64_t B, int64_t K,
+                 int64_t N, int act, int out_dtype, cudaStream_t st);
+int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int64_t B, int64_t K,
+            int64_t N, int act_prev, cudaStream_t st);
+// Split-K plan for dW on tcgen05; splits == 1 means the SGD/store epilogue is fused.
+int umma_dw_splits(int64_t B, int64_t K, int64_t N);
+int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_master,
+            bf16* W_shadow, float* dW_out, float lr, int apply, int64_t B, int64_t K, int64_t N,
+            cudaStream_t st);
+
+}  // namespace ddnn

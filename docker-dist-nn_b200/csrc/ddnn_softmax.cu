@@ -1,0 +1,231 @@
+// Row softmax (grpc_node.py:68-71), softmax cross-entropy with fused dZ, elementwise
+// activations (grpc_node.py:62-67) and dtype casts.  All HBM-bound: one read of Z from
+// DRAM (re-reads hit L1/L2), one write per output, warp-shuffle reductions.
+#include "ddnn_internal.h"
+
+namespace ddnn {
+namespace {
+
+template <int G>
+__device__ __forceinline__ float group_max(float v) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+template <int G>
+__device__ __forceinline__ float group_sum(float v) {
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// N <= 1024: G lanes cooperate on one row, 256/G rows per CTA.
+template <int G, typename TD>
+__global__ void __launch_bounds__(256)
+softmax_group_kernel(const float* __restrict__ Z, const int32_t* __restrict__ labels, float* __restrict__ P,
+                     TD* __restrict__ dZ, float* __restrict__ row_loss, int64_t B, int N, float inv_denom) {
+  const int gl = threadIdx.x % G;
+  const int64_t row = (int64_t)blockIdx.x * (256 / G) + threadIdx.x / G;
+  const bool valid = row < B;
+  const int64_t rc = valid ? row : (B - 1);
+  const float* z = Z + rc * N;
+  float m = -INFINITY;
+  for (int c = gl; c < N; c += G) m = fmaxf(m, z[c]);
+  m = group_max<G>(m);
+  float s = 0.f;
+  for (int c = gl; c < N; c += G) s += expf(z[c] - m);
+  s = group_sum<G>(s);
+  const float inv = 1.0f / s;
+  int y = -1;
+  if (labels) y = labels[rc];
+  if (valid && row_loss && gl == 0) {
+    float l = 0.f;
+    if (y >= 0 && y < N) l = -((z[y] - m) - logf(s));
+    row_loss[row] = l;
+  }
+  if (!valid) return;
+  for (int c = gl; c < N; c += G) {
+    const float p = expf(z[c] - m) * inv;
+    if (P) P[row * N + c] = p;
+    if (dZ) dZ[row * N + c] = from_f32<TD>((p - (c == y ? 1.0f : 0.0f)) * inv_denom);
+  }
+}
+
+__device__ __forceinline__ float block_reduce(float v, bool is_max, float* sh) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = is_max ? warp_max(v) : warp_sum(v);
+  __syncthreads();  // protect sh reuse
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  float r = sh[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) r = is_max ? fmaxf(r, sh[w]) : r + sh[w];
+  return r;
+}
+
+// N > 1024: one 256-thread CTA per row, float4 accesses when N % 4 == 0.
+template <typename TD>
+__global__ void __launch_bounds__(256)
+softmax_block_kernel(const float* __restrict__ Z, const int32_t* __restrict__ labels, float* __restrict__ P,
+                     TD* __restrict__ dZ, float* __restrict__ row_loss, int64_t B, int N, float inv_denom, bool vec) {
+  __shared__ float sh[8];
+  const int64_t row = blockIdx.x;
+  const float* z = Z + row * N;
+  const int t = threadIdx.x;
+  float m = -INFINITY;
+  if (vec) {
+    for (int c = t * 4; c < N; c += 1024) {
+      float4 v = ld4(z + c);
+      m = fmaxf(fmaxf(m, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+    }
+  } else {
+    for (int c = t; c < N; c += 256) m = fmaxf(m, z[c]);
+  }
+  m = block_reduce(m, true, sh);
+  float s = 0.f;
+  if (vec) {
+    for (int c = t * 4; c < N; c += 1024) {
+      float4 v = ld4(z + c);
+      s += expf(v.x - m) + expf(v.y - m) + expf(v.z - m) + expf(v.w - m);
+    }
+  } else {
+    for (int c = t; c < N; c += 256) s += expf(z[c] - m);
+  }
+  s = block_reduce(s, false, sh);
+  const float inv = 1.0f / s;
+  int y = -1;
+  if (labels) y = labels[row];
+  if (row_loss && t == 0) {
+    float l = 0.f;
+    if (y >= 0 && y < N) l = -((z[y] - m) - logf(s));
+    row_loss[row] = l;
+  }
+  if (vec) {
+    for (int c = t * 4; c < N; c += 1024) {
+      float4 v = ld4(z + c);
+      float4 p = make_float4(expf(v.x - m) * inv, expf(v.y - m) * inv, expf(v.z - m) * inv, expf(v.w - m) * inv);
+      if (P) st4(P + row * N + c, p);
+      if (dZ) {
+        float4 d = make_float4((p.x - (c == y ? 1.f : 0.f)) * inv_denom, (p.y - (c + 1 == y ? 1.f : 0.f)) * inv_denom,
+                               (p.z - (c + 2 == y ? 1.f : 0.f)) * inv_denom, (p.w - (c + 3 == y ? 1.f : 0.f)) * inv_denom);
+        st4(dZ + row * N + c, d);
+      }
+    }
+  } else {
+    for (int c = t; c < N; c += 256) {
+      const float p = expf(z[c] - m) * inv;
+      if (P) P[row * N + c] = p;
+      if (dZ) dZ[row * N + c] = from_f32<TD>((p - (c == y ? 1.0f : 0.0f)) * inv_denom);
+    }
+  }
+}
+
+// loss (+)= scale * sum(row_loss) -- single CTA, fixed summation tree => deterministic
+__global__ void __launch_bounds__(1024)
+loss_reduce_kernel(const float* __restrict__ row_loss, float* __restrict__ loss, int64_t B, float scale, int accumulate) {
+  __shared__ float sh[32];
+  float s = 0.f;
+  for (int64_t i = threadIdx.x; i < B; i += 1024) s += row_loss[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float v = sh[threadIdx.x];
+    v = warp_sum(v);
+    if (threadIdx.x == 0) *loss = (accumulate ? *loss : 0.f) + v * scale;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+activate_kernel(const float* __restrict__ in, float* __restrict__ out, int64_t n, int act) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = act_fwd(in[i], act);
+}
+
+template <typename TI, typename TO>
+__global__ void __launch_bounds__(256) cast_kernel(const TI* __restrict__ in, TO* __restrict__ out, int64_t n) {
+  const int64_t n4 = n >> 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x)
+    st4(out + i * 4, ld4(in + i * 4));
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const int64_t i = (n4 << 2) + threadIdx.x;
+    out[i] = from_f32<TO>(to_f32(in[i]));
+  }
+}
+
+template <typename TD>
+int launch_softmax(const float* Z, const int32_t* labels, float* P, TD* dZ, float* row_loss, int64_t B, int N,
+                   float inv_denom, cudaStream_t st) {
+  if (N <= 1024) {
+#define DDNN_SM_GROUP(G)                                                                                   \
+  softmax_group_kernel<G, TD><<<cdiv(B, 256 / G), 256, 0, st>>>(Z, labels, P, dZ, row_loss, B, N, inv_denom)
+    if (N <= 4) DDNN_SM_GROUP(4);
+    else if (N <= 8) DDNN_SM_GROUP(8);
+    else if (N <= 16) DDNN_SM_GROUP(16);
+    else DDNN_SM_GROUP(32);
+#undef DDNN_SM_GROUP
+  } else {
+    bool vec = (N % 4 == 0) && (reinterpret_cast<uintptr_t>(Z) % 16 == 0) &&
+               (!P || reinterpret_cast<uintptr_t>(P) % 16 == 0) &&
+               (!dZ || reinterpret_cast<uintptr_t>(dZ) % (4 * sizeof(TD)) == 0);
+    softmax_block_kernel<TD><<<(unsigned)B, 256, 0, st>>>(Z, labels, P, dZ, row_loss, B, N, inv_denom, vec);
+  }
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+
+int grid_for(int64_t n) {
+  int64_t b = (n + 255) / 256;
+  if (b > 148 * 16) b = 148 * 16;
+  return (int)(b < 1 ? 1 : b);
+}
+
+}  // namespace
+
+int softmax_rows(const float* Z, float* P, int64_t B, int64_t N, cudaStream_t st) {
+  return launch_softmax<float>(Z, nullptr, P, nullptr, nullptr, B, (int)N, 0.f, st);
+}
+
+int softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ, float* row_loss, float* loss, int64_t B,
+               int64_t N, float inv_denom, int dz_dtype, int accumulate, cudaStream_t st) {
+  int rc;
+  if (dz_dtype == DDNN_F32)
+    rc = launch_softmax<float>(Z, labels, P, (float*)dZ, row_loss, B, (int)N, inv_denom, st);
+  else if (dz_dtype == DDNN_BF16)
+    rc = launch_softmax<bf16>(Z, labels, P, (bf16*)dZ, row_loss, B, (int)N, inv_denom, st);
+  else {
+    set_error("softmax_ce: unsupported dZ dtype %d", dz_dtype);
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  if (rc != DDNN_OK) return rc;
+  if (loss && row_loss) {
+    loss_reduce_kernel<<<1, 1024, 0, st>>>(row_loss, loss, B, inv_denom, accumulate);
+    count_launch();
+    DDNN_LAUNCH_CHECK();
+  }
+  return DDNN_OK;
+}
+
+int activate(const float* V, float* out, int64_t B, int64_t N, int act, cudaStream_t st) {
+  if (act == DDNN_ACT_SOFTMAX) return softmax_rows(V, out, B, N, st);
+  activate_kernel<<<grid_for(B * N), 256, 0, st>>>(V, out, B * N, act);
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+
+int cast_f32_bf16(const float* in, bf16* out, int64_t n, cudaStream_t st) {
+  cast_kernel<float, bf16><<<grid_for(n / 4 + 1), 256, 0, st>>>(in, out, n);
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+int cast_bf16_f32(const bf16* in, float* out, int64_t n, cudaStream_t st) {
+  cast_kernel<bf16, float><<<grid_for(n / 4 + 1), 256, 0, st>>>(in, out, n);
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+
+}  // namespace ddnn

@@ -1,0 +1,549 @@
+// bf16 GEMM family on the 5th-generation tensor cores: tcgen05.mma with the accumulator in
+// TMEM, operands staged by TMA into 128B-swizzled shared memory, persistent warp-specialised
+// CTAs (one per SM):  warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread),
+// warp 2 = TMEM allocator, warps 4-7 = epilogue (TMEM -> registers -> fused epilogue -> HBM).
+// Two accumulator stages in TMEM let the epilogue of tile i overlap the MMAs of tile i+1.
+//
+// Three operand layouts, chosen by descriptor major-ness instead of transposing in memory:
+//   forward  Z = X.W      D[B,N]  : A = X  (K-major),  B = W  (MN-major, W is [K][N] like grpc_node.py:51)
+//   dX       dA = dZ.W^T  D[B,K]  : A = dZ (K-major),  B = W  (K-major: the reduction runs over W's rows)
+//   dW       dW = X^T.dZ  D[K,N]  : A = X  (MN-major), B = dZ (MN-major), reduction over the batch
+// Fused epilogues: bias + activation (forward), activation derivative (dX), SGD update with
+// fp32 master + bf16 shadow write (dW), or fp32 store (gradient output / split-K partial).
+#include <cuda.h>
+
+#include <mutex>
+#include <unordered_map>
+
+#include "ddnn_internal.h"
+
+namespace ddnn {
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B row
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 256;
+constexpr int GROUP_M = 8;  // m-blocks per rasterisation group (L2 reuse of the B operand)
+
+enum { EPI_FWD_BF16 = 0, EPI_FWD_F32 = 1, EPI_DX = 2, EPI_SGD = 3, EPI_STORE = 4 };
+
+struct UmmaParams {
+  int M, N;  // output tile space (rows, cols)
+  int m_blocks, n_blocks, num_kb, splits, kb_per_split;
+  const float* bias;
+  int act;
+  void* out;
+  const bf16* aprev;
+  float* w_master;
+  bf16* w_shadow;
+  float lr;
+  int64_t zrows;  // row offset per split for EPI_STORE partials
+};
+
+// ---- PTX wrappers -------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "WAIT_LOOP:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra WAIT_LOOP;\n"
+      "DONE:\n"
+      "}\n" ::"r"(bar), "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] . B[smem]   (bf16 x bf16 -> fp32), issued by ONE thread for the CTA
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+// arrives on `bar` when all previously issued tcgen05.mma of this thread have completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+// 32 lanes x 32 columns of fp32: thread i of the warp gets TMEM lane (base_lane + i), columns c..c+31
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- descriptors --------------------------------------------------------------------
+// Shared-memory matrix descriptor (sm_100): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) |
+// version=1 [46,48) | layout [61,64) (2 = SWIZZLE_128B).
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= 1ull << 46;
+  d |= 2ull << 61;
+  return d;
+}
+// K-major tile [rows][64] (row = 128 B, 8-row swizzle atoms 1024 B apart): step k by 32 bytes.
+// MN-major tile: 64-element MN atoms, each [64 k][64 mn] (k row = 128 B): 8-k groups 1024 B apart
+// (SBO), MN atoms 8192 B apart (LBO); step k (16 rows) by 2048 bytes.
+template <bool MN_MAJOR>
+__device__ __forceinline__ uint64_t operand_desc(uint32_t tile_base, int k) {
+  if (MN_MAJOR) return make_desc(tile_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024);
+  return make_desc(tile_base + k * (UMMA_K * 2), 0, 1024);
+}
+// Instruction descriptor, kind::f16: D=f32 [4,6)=1, A=bf16 [7,10)=1, B=bf16 [10,13)=1,
+// a_major bit 15, b_major bit 16 (1 = MN-major), N>>3 [17,23), M>>4 [24,29).
+template <bool A_MN, bool B_MN, int BN>
+__device__ __forceinline__ constexpr uint32_t instr_desc() {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+         ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+}
+
+template <int BN>
+struct Cfg {
+  static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
+  static constexpr uint32_t B_BYTES = BN * BLOCK_K * 2;
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr uint32_t TMEM_COLS = 2 * BN;
+  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + (2 * STAGES + 4) * 8 + 16;
+};
+
+struct TileCoord {
+  int m_blk, n_blk, ks, kb0, kb1;
+};
+__device__ __forceinline__ TileCoord decode_tile(int tile, const UmmaParams& p) {
+  TileCoord t;
+  const int per_split = p.m_blocks * p.n_blocks;
+  t.ks = tile / per_split;
+  const int rem = tile - t.ks * per_split;
+  const int group_sz = GROUP_M * p.n_blocks;
+  const int gid = rem / group_sz;
+  const int first_m = gid * GROUP_M;
+  const int gm = min(p.m_blocks - first_m, GROUP_M);
+  const int in_g = rem - gid * group_sz;
+  t.m_blk = first_m + in_g % gm;
+  t.n_blk = in_g / gm;
+  t.kb0 = t.ks * p.kb_per_split;
+  t.kb1 = min(p.num_kb, t.kb0 + p.kb_per_split);
+  return t;
+}
+
+template <bool A_MN, bool B_MN, int BN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 const UmmaParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
+  const uint32_t bars = tiles + C::STAGES * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * C::STAGES + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * C::STAGES + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * C::STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);  // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord t = decode_tile(tile, p);
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
+          const uint32_t a_dst = tiles + stage * C::STAGE_BYTES;
+          const uint32_t b_dst = a_dst + C::A_BYTES;
+          if (!A_MN) {
+            tma_load_2d(a_dst, &tma_a, full_bar(stage), kb * BLOCK_K, t.m_blk * BLOCK_M);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BLOCK_M / 64; ++i)
+              tma_load_2d(a_dst + i * (BLOCK_K * 128), &tma_a, full_bar(stage), t.m_blk * BLOCK_M + i * 64,
+                          kb * BLOCK_K);
+          }
+          if (!B_MN) {
+            tma_load_2d(b_dst, &tma_b, full_bar(stage), kb * BLOCK_K, t.n_blk * BN);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 64; ++i)
+              tma_load_2d(b_dst + i * (BLOCK_K * 128), &tma_b, full_bar(stage), t.n_blk * BN + i * 64, kb * BLOCK_K);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = instr_desc<A_MN, B_MN, BN>();
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord t = decode_tile(tile, p);
+        mbar_wait(tempty_bar(as), aphase ^ 1);  // epilogue has drained this accumulator stage
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);  // TMA bytes have landed
+          tc_fence_after();
+          const uint32_t a_base = tiles + stage * C::STAGE_BYTES;
+          const uint32_t b_base = a_base + C::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_bf16(d_tmem, operand_desc<A_MN>(a_base, k), operand_desc<B_MN>(b_base, k), idesc,
+                      (kb > t.kb0 || k > 0) ? 1u : 0u);
+          umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs finish
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tfull_bar(as));  // accumulator complete -> epilogue
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    uint32_t as = 0, aphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord t = decode_tile(tile, p);
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const int row = t.m_blk * BLOCK_M + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      const int64_t orow = (int64_t)row + (EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        tmem_ld32(tmem_base + as * BN + c * 32 + ((uint32_t)(q * 32) << 16), v);
+        tmem_ld_wait();
+        const int col0 = t.n_blk * BN + c * 32;
+        if (row_ok) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const int col = col0 + j * 4;
+            if (col < p.N) {
+              const float4 x = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              if (EPI == EPI_FWD_BF16) {
+                EpiFwd<bf16>{p.bias, (bf16*)p.out, p.N, p.act}.apply4(orow, col, x, 4, true);
+              } else if (EPI == EPI_FWD_F32) {
+                EpiFwd<float>{p.bias, (float*)p.out, p.N, p.act}.apply4(orow, col, x, 4, true);
+              } else if (EPI == EPI_DX) {
+                EpiDx<bf16>{p.aprev, (bf16*)p.out, p.N, p.act}.apply4(orow, col, x, 4, true);
+              } else if (EPI == EPI_SGD) {
+                EpiSgd{p.w_master, p.w_shadow, p.N, p.lr}.apply4(orow, col, x, 4, true);
+              } else {
+                EpiStoreF32{(float*)p.out, p.N}.apply4(orow, col, x, 4, true);
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(as));
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(f);
+  });
+  return fn;
+}
+
+struct TmapKey {
+  const void* ptr;
+  uint64_t inner, outer;
+  uint32_t b0, b1;
+  bool operator==(const TmapKey& o) const {
+    return ptr == o.ptr && inner == o.inner && outer == o.outer && b0 == o.b0 && b1 == o.b1;
+  }
+};
+struct TmapHash {
+  size_t operator()(const TmapKey& k) const {
+    size_t h = std::hash<const void*>()(k.ptr);
+    h = h * 1000003u ^ std::hash<uint64_t>()(k.inner);
+    h = h * 1000003u ^ std::hash<uint64_t>()(k.outer);
+    h = h * 1000003u ^ (((size_t)k.b0 << 16) | k.b1);
+    return h;
+  }
+};
+std::mutex g_tmap_mu;
+std::unordered_map<TmapKey, CUtensorMap, TmapHash> g_tmaps;
+
+// bf16 row-major [outer][inner]; box {b0 along inner, b1 along outer}; 128B swizzle; OOB -> 0
+int get_tmap(const bf16* ptr, uint64_t inner, uint64_t outer, uint32_t b0, uint32_t b1, CUtensorMap* out) {
+  TmapKey key{ptr, inner, outer, b0, b1};
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mu);
+    auto it = g_tmaps.find(key);
+    if (it != g_tmaps.end()) {
+      *out = it->second;
+      return DDNN_OK;
+    }
+  }
+  EncodeTiledFn enc = get_encode();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled is not available from this driver");
+    return DDNN_ERR_CUDA;
+  }
+  cuuint64_t gdim[2] = {inner, outer};
+  cuuint64_t gstride[1] = {inner * sizeof(bf16)};
+  cuuint32_t box[2] = {b0, b1};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<bf16*>(ptr), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) ptr=%p inner=%llu outer=%llu box=%ux%u", (int)r, (const void*)ptr,
+              (unsigned long long)inner, (unsigned long long)outer, b0, b1);
+    return DDNN_ERR_CUDA;
+  }
+  {
+    std::lock_guard<std::mutex> g(g_tmap_mu);
+    if (g_tmaps.size() > 4096) g_tmaps.clear();
+    g_tmaps[key] = m;
+  }
+  *out = m;
+  return DDNN_OK;
+}
+
+int num_sms() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = 148;
+  }
+  return n;
+}
+
+int pick_bn(int64_t n) { return n >= 192 ? 256 : (n >= 96 ? 128 : 64); }
+
+template <bool A_MN, bool B_MN, int BN, int EPI>
+int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p, cudaStream_t st) {
+  auto kern = umma_gemm_kernel<A_MN, B_MN, BN, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int total = p.m_blocks * p.n_blocks * p.splits;
+  const int grid = total < num_sms() ? total : num_sms();
+  kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, st>>>(ta, tb, p);
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p, cudaStream_t st) {
+  if (bn == 256) return launch_one<A_MN, B_MN, 256, EPI>(ta, tb, p, st);
+  if (bn == 128) return launch_one<A_MN, B_MN, 128, EPI>(ta, tb, p, st);
+  return launch_one<A_MN, B_MN, 64, EPI>(ta, tb, p, st);
+}
+
+// A operand map: K-major -> stored [M][Kred], box {64, 128}; MN-major -> stored [Kred][M], box {64, 64}
+int operand_maps(bool a_mn, const bf16* A, bool b_mn, const bf16* Bm, int64_t M, int64_t N, int64_t Kred, int bn,
+                 CUtensorMap* ta, CUtensorMap* tb) {
+  int rc = a_mn ? get_tmap(A, M, Kred, 64, 64, ta) : get_tmap(A, Kred, M, 64, BLOCK_M, ta);
+  if (rc != DDNN_OK) return rc;
+  return b_mn ? get_tmap(Bm, N, Kred, 64, 64, tb) : get_tmap(Bm, Kred, N, 64, bn, tb);
+}
+
+void fill_tiles(UmmaParams& p, int64_t M, int64_t N, int64_t Kred, int bn, int splits) {
+  p.M = (int)M;
+  p.N = (int)N;
+  p.m_blocks = cdiv(M, BLOCK_M);
+  p.n_blocks = cdiv(N, bn);
+  p.num_kb = cdiv(Kred, BLOCK_K);
+  if (p.num_kb < 1) p.num_kb = 1;
+  if (splits < 1) splits = 1;
+  p.kb_per_split = cdiv(p.num_kb, splits);
+  p.splits = cdiv(p.num_kb, p.kb_per_split);  // every split owns >= 1 k-block
+}
+
+}  // namespace
+
+bool umma_shape_ok(int64_t B, int64_t K, int64_t N) { return B > 0 && K >= 8 && N >= 8 && K % 8 == 0 && N % 8 == 0; }
+
+int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64_t B, int64_t K, int64_t N, int act,
+                 int out_dtype, cudaStream_t st) {
+  const int bn = pick_bn(N);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(false, X, true, W, B, N, K, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  UmmaParams p{};
+  fill_tiles(p, B, N, K, bn, 1);
+  p.bias = bias;
+  p.act = act;
+  p.out = A;
+  if (out_dtype == DDNN_BF16) return launch_bn<false, true, EPI_FWD_BF16>(bn, ta, tb, p, st);
+  return launch_bn<false, true, EPI_FWD_F32>(bn, ta, tb, p, st);
+}
+
+int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int64_t B, int64_t K, int64_t N,
+            int act_prev, cudaStream_t st) {
+  // D[B, K] = dZ[B, N] . W[K, N]^T : GEMM-N = K (layer input width), reduction = N
+  const int bn = pick_bn(K);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(false, dZ, false, W, B, K, N, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  UmmaParams p{};
+  fill_tiles(p, B, K, N, bn, 1);
+  p.act = act_prev;
+  p.aprev = Aprev;
+  p.out = dZprev;
+  return launch_bn<false, false, EPI_DX>(bn, ta, tb, p, st);
+}
+
+int umma_dw_splits(int64_t B, int64_t K, int64_t N) {
+  const int bn = pick_bn(N);
+  const long tiles = (long)cdiv(K, BLOCK_M) * cdiv(N, bn);
+  if (tiles >= num_sms()) return 1;
+  const int num_kb = cdiv(B, BLOCK_K);
+  long want = (num_sms() + tiles - 1) / tiles;
+  long max_by_k = num_kb / 4;  // >= 4 k-blocks per split
+  if (max_by_k < 1) max_by_k = 1;
+  long s = want < max_by_k ? want : max_by_k;
+  if (s < 1) s = 1;
+  const int per = cdiv(num_kb, s);
+  return cdiv(num_kb, per);
+}
+
+int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_master, bf16* W_shadow, float* dW_out,
+            float lr, int apply, int64_t B, int64_t K, int64_t N, cudaStream_t st) {
+  // D[K, N] = X[B, K]^T . dZ[B, N] : GEMM-M = K, GEMM-N = N, reduction = B
+  const int bn = pick_bn(N);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(true, X, true, dZ, K, N, B, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  UmmaParams p{};
+  fill_tiles(p, K, N, B, bn, splits);
+  if (p.splits > 1) {
+    if (p.splits != splits) {
+      set_error("umma_dw: split plan mismatch (%d vs %d)", p.splits, splits);
+      return DDNN_ERR_ARG;
+    }
+    p.out = dw_part;
+    p.zrows = K;
+    return launch_bn<true, true, EPI_STORE>(bn, ta, tb, p, st);
+  }
+  if (apply) {
+    p.w_master = W_master;
+    p.w_shadow = W_shadow;
+    p.lr = lr;
+    return launch_bn<true, true, EPI_SGD>(bn, ta, tb, p, st);
+  }
+  p.out = dW_out;
+  p.zrows = 0;
+  return launch_bn<true, true, EPI_STORE>(bn, ta, tb, p, st);
+}
+
+}  // namespace ddnn

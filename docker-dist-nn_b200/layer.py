@@ -1,0 +1,283 @@
+"""``Layer`` -- the node/layer API of /root/reference/src/grpc_node.py:16-97 on a B200.
+
+Same constructor contract (environment variables CONTAINER_NAME, LISTEN_PORT,
+EXPECTED_INPUT_DIM, NEURONS_CONFIG | NEURONS_FILE_CONFIG, NEXT_NODES), same attributes
+(``container_name, listen_port, expected_input_dim, layer_params, next_nodes``), same
+methods (``activate``, ``process_matrix``) with the same error text; the arithmetic runs
+in libddnn.so.  ``layer_params[i]["weights"]`` stays (K, N) like grpc_node.py:51 but is a
+CUDA fp32 tensor (the master copy the SGD epilogue updates in place).
+
+Added for training (no reference counterpart): ``begin_batch``,
+``forward_train``, ``loss_and_grad``, ``backward``, ``step``, ``gradients``.
+"""
+from __future__ import annotations
+
+import json
+import os
+import sys
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib, ops
+from .config import node_config_to_params
+
+_TORCH_DT = {"f32": torch.float32, "fp32": torch.float32, "float32": torch.float32,
+             "bf16": torch.bfloat16, "bfloat16": torch.bfloat16}
+
+
+def _device(device) -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError("docker-dist-nn_b200 needs a CUDA device (B200, sm_100a); there is no CPU fallback")
+    if device is None:
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device(device)
+
+
+class Layer:
+    def __init__(self, dtype: Optional[str] = None, device=None):
+        # grpc_node.py:17-58 -- identical environment contract and failure behaviour
+        self.container_name = os.environ.get("CONTAINER_NAME", "layer")
+        self.listen_port = int(os.environ.get("LISTEN_PORT", "8000"))
+        self.expected_input_dim = int(os.environ.get("EXPECTED_INPUT_DIM", "0"))
+        neurons_config_data = None
+        if "NEURONS_CONFIG" in os.environ:
+            neurons_config_data = json.loads(os.environ["NEURONS_CONFIG"])
+            print(f"({self.container_name}) Loaded neurons config from env var.")
+        elif "NEURONS_FILE_CONFIG" in os.environ:
+            config_path = os.environ["NEURONS_FILE_CONFIG"]
+            try:
+                with open(config_path, "r") as f:
+                    neurons_config_data = json.load(f)
+                print(f"({self.container_name}) Loaded neurons config from file: {config_path}")
+            except FileNotFoundError:
+                print(f"({self.container_name}) ERROR: Neurons config file not found at {config_path}")
+                sys.exit(1)
+            except json.JSONDecodeError:
+                print(f"({self.container_name}) ERROR: Failed to decode JSON from {config_path}")
+                sys.exit(1)
+        else:
+            print(f"({self.container_name}) ERROR: No neuron configuration provided "
+                  "(NEURONS_CONFIG or NEURONS_FILE_CONFIG env var).")
+            sys.exit(1)
+        self.next_nodes = json.loads(os.environ.get("NEXT_NODES", "[]"))
+        self._init(node_config_to_params(neurons_config_data or {}),
+                   dtype or os.environ.get("DDNN_DTYPE", "f32"), device, "linear", None)
+        print(f"({self.container_name}) Initialized {len(self.layer_params)} layer(s).")
+
+    # -- programmatic constructor (benchmarks build multi-GiB layers from a seed, not JSON) --
+    @classmethod
+    def from_params(cls, layer_params: Sequence[Dict[str, Any]], expected_input_dim: int,
+                    container_name: str = "layer", next_nodes: Optional[list] = None, dtype: str = "f32",
+                    device=None, input_activation: str = "linear", is_output: Optional[bool] = None,
+                    listen_port: int = 8000) -> "Layer":
+        self = cls.__new__(cls)
+        self.container_name = container_name
+        self.listen_port = listen_port
+        self.expected_input_dim = int(expected_input_dim)
+        self.next_nodes = list(next_nodes or [])
+        self._init(layer_params, dtype, device, input_activation, is_output)
+        return self
+
+    def _init(self, params, dtype, device, input_activation, is_output) -> None:
+        self.device = _device(device)
+        self.dtype = "bf16" if _TORCH_DT[dtype] == torch.bfloat16 else "f32"
+        self._cdt = _TORCH_DT[dtype]
+        # activation of the layer feeding this node (its derivative is fused into our dX)
+        self.input_activation = input_activation
+        # the last node of the chain owns the loss (grpc_node.py:143: no next_nodes)
+        self.is_output = (not self.next_nodes) if is_output is None else bool(is_output)
+        self.layer_params: List[Dict[str, Any]] = []
+        self._shadow: List[Optional[torch.Tensor]] = []
+        for p in params:
+            w = self._to_dev(p["weights"])
+            b = self._to_dev(p["biases"])
+            if w.dim() != 2 or b.numel() != w.shape[1]:
+                raise ValueError("weights must be (in, out) with one bias per output")
+            self.layer_params.append({"weights": w, "biases": b, "activation": p.get("activation", "linear")})
+            self._shadow.append(ops.cast(w, torch.bfloat16) if self._cdt == torch.bfloat16 else None)
+        self._rows = 0
+        self._bufs = None
+        self._ws = None
+
+    def _to_dev(self, t) -> torch.Tensor:
+        """numpy / list / torch (any device) -> contiguous fp32 tensor on this node's GPU."""
+        if isinstance(t, torch.Tensor):
+            return t.detach().to(device=self.device, dtype=torch.float32).contiguous()
+        return torch.as_tensor(np.asarray(t), dtype=torch.float32).contiguous().to(self.device)
+
+    @property
+    def wire_dtype(self) -> torch.dtype:
+        """Element type of the activations / gradients exchanged between stages."""
+        return self._cdt
+
+    # ------------------------------------------------------------------ inference
+    def activate(self, values, func: str):
+        """grpc_node.py:62-73 on the GPU.  numpy in -> numpy (float64) out; CUDA tensor in ->
+        CUDA fp32 tensor out.  Unknown ``func`` strings are the identity."""
+        is_np = isinstance(values, np.ndarray)
+        v = torch.as_tensor(values, dtype=torch.float32).to(self.device) if is_np else values.float()
+        squeeze = v.dim() == 1
+        v2 = (v.unsqueeze(0) if squeeze else v).contiguous()
+        out = ops.activate(v2, func) if v2.numel() else v2.clone()
+        out = out.squeeze(0) if squeeze else out
+        return out.double().cpu().numpy() if is_np else out
+
+    def _w(self, i: int) -> torch.Tensor:
+        return self._shadow[i] if self._cdt == torch.bfloat16 else self.layer_params[i]["weights"]
+
+    def _check_dim(self, i: int, got: int, expected: int) -> None:
+        if got != expected or got != self.layer_params[i]["weights"].shape[0]:
+            exp = expected if got != expected else self.layer_params[i]["weights"].shape[0]
+            raise ValueError(f"({self.container_name}) Layer {i + 1}: expected input dim {exp}, got {got}")
+
+    def process_matrix(self, input_matrix):
+        """grpc_node.py:75-97: chain ``act(X.W + b)`` over this node's layers.  Accepts a 2-D
+        numpy array (returns float64 numpy, like the reference) or a CUDA tensor (returns a
+        CUDA fp32 tensor).  Raises the reference's ValueError on a width mismatch."""
+        is_np = isinstance(input_matrix, np.ndarray)
+        cur = (torch.as_tensor(input_matrix, dtype=torch.float32).to(self.device) if is_np else input_matrix)
+        if cur.dim() != 2:
+            raise ValueError(f"({self.container_name}) input must be 2-D (rows, features)")
+        cur = cur.contiguous()
+        if cur.dtype != self._cdt:
+            cur = ops.cast(cur, self._cdt) if cur.numel() else cur.to(self._cdt)
+        expected = self.expected_input_dim
+        n_layers = len(self.layer_params)
+        for i, p in enumerate(self.layer_params):
+            self._check_dim(i, cur.shape[1], expected)
+            act = p["activation"]
+            last = i == n_layers - 1
+            if cur.shape[0] == 0:  # empty request -> empty result (grpc_node.py:108-111)
+                cur = torch.empty((0, p["weights"].shape[1]), dtype=self._cdt, device=self.device)
+            elif act == "softmax" or (last and self.is_output):
+                out = ops.dense_forward(cur, self._w(i), p["biases"], act, out_dtype=torch.float32)
+                cur = out if last else (ops.cast(out, self._cdt) if self._cdt != torch.float32 else out)
+            else:
+                cur = ops.dense_forward(cur, self._w(i), p["biases"], act)
+            expected = cur.shape[1]
+        out = cur if cur.dtype == torch.float32 else (ops.cast(cur.contiguous(), torch.float32) if cur.numel()
+                                                      else cur.float())
+        return out.double().cpu().numpy() if is_np else out
+
+    # ------------------------------------------------------------------ training
+    def begin_batch(self, rows: int) -> None:
+        """(Re)allocates the per-batch buffers: layer inputs A[l], pre-softmax logits Z of
+        an output node (fp32), one dZ per local layer, the gradient handed upstream, the
+        split-K workspace.  Buffers are reused while ``rows`` does not grow."""
+        if self._bufs is not None and rows <= self._bufs["cap"]:
+            self._rows = rows
+            return
+        dev, cdt = self.device, self._cdt
+        lp = self.layer_params
+        a = [torch.empty((rows, lp[0]["weights"].shape[0]), dtype=cdt, device=dev)]
+        dz = []
+        for i, p in enumerate(lp):
+            n = p["weights"].shape[1]
+            last = i == len(lp) - 1
+            a.append(torch.empty((rows, n), dtype=torch.float32 if (last and self.is_output) else cdt, device=dev))
+            dz.append(torch.empty((rows, n), dtype=cdt, device=dev))
+        ws_bytes = max(ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp)
+        self._bufs = {
+            "cap": rows, "a": a, "dz": dz,
+            "dx": torch.empty((rows, lp[0]["weights"].shape[0]), dtype=cdt, device=dev),
+            "row_loss": torch.empty((rows,), dtype=torch.float32, device=dev),
+            "loss": torch.zeros((1,), dtype=torch.float32, device=dev),
+        }
+        self._ws = torch.empty((max(ws_bytes, 256),), dtype=torch.uint8, device=dev)
+        self._rows = rows
+
+    def input_buffer(self, row0: int, rows: int) -> torch.Tensor:
+        """Rows [row0, row0+rows) of this node's input activation buffer (receive target)."""
+        return self._bufs["a"][0][row0:row0 + rows]
+
+    def grad_buffer(self, row0: int, rows: int) -> torch.Tensor:
+        """Rows of dZ of the LAST local layer (receive target for the downstream gradient)."""
+        return self._bufs["dz"][-1][row0:row0 + rows]
+
+    def output_buffer(self, row0: int, rows: int) -> torch.Tensor:
+        return self._bufs["a"][-1][row0:row0 + rows]
+
+    def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None) -> torch.Tensor:
+        """Forward of rows [row0, row0+rows) keeping what backward needs.  ``x`` None means the
+        rows are already in ``input_buffer``.  An output node stops at the fp32 logits Z
+        (softmax is fused into ``loss_and_grad``)."""
+        a = self._bufs["a"]
+        if x is not None:
+            rows = x.shape[0]
+            if x.shape[1] != self.expected_input_dim:
+                raise ValueError(f"({self.container_name}) Layer 1: expected input dim {self.expected_input_dim}, "
+                                 f"got {x.shape[1]}")
+            dst = a[0][row0:row0 + rows]
+            if x.dtype == self._cdt:
+                dst.copy_(x)
+            else:
+                ops.cast(x.contiguous(), self._cdt, out=dst)
+        n_layers = len(self.layer_params)
+        for i, p in enumerate(self.layer_params):
+            last = i == n_layers - 1
+            act = p["activation"]
+            if last and self.is_output:
+                if act in ("relu", "sigmoid"):
+                    raise ValueError(f"output activation {act!r} has no softmax-CE loss")
+                act = "linear"  # logits; softmax happens inside the fused CE kernel
+            elif act == "softmax":
+                raise ValueError("hidden softmax layers are not supported in training (row Jacobian)")
+            ops.dense_forward(a[i][row0:row0 + rows], self._w(i), p["biases"], act, out=a[i + 1][row0:row0 + rows])
+        return a[-1][row0:row0 + rows]
+
+    def loss_and_grad(self, labels: torch.Tensor, row0: int = 0, denom: Optional[int] = None,
+                      accumulate: bool = False) -> torch.Tensor:
+        """Softmax-CE on the logits of rows [row0, row0+len(labels)); fills dZ of the last
+        layer with (p - onehot)/denom and (adds to) the device loss scalar.  ``denom`` =
+        global batch size (default: the rows of this call)."""
+        if not self.is_output:
+            raise RuntimeError("loss_and_grad is only defined on the output node")
+        rows = labels.numel()
+        denom = rows if denom is None else denom
+        b = self._bufs
+        ops.softmax_ce(b["a"][-1][row0:row0 + rows], labels, b["dz"][-1][row0:row0 + rows],
+                       b["row_loss"][row0:row0 + rows], b["loss"], 1.0 / float(denom), accumulate=accumulate)
+        return b["loss"]
+
+    def backward(self, row0: int = 0, rows: Optional[int] = None, need_input_grad: bool = True
+                 ) -> Optional[torch.Tensor]:
+        """dX chain for rows [row0, row0+rows): dZ[l-1] = (dZ[l].W_l^T) * f'_{l-1}(A[l]).  Returns
+        dZ for the node feeding this one (already multiplied by that node's activation
+        derivative, ``input_activation``) or None when ``need_input_grad`` is False."""
+        rows = self._rows - row0 if rows is None else rows
+        b = self._bufs
+        sl = slice(row0, row0 + rows)
+        for i in range(len(self.layer_params) - 1, 0, -1):
+            ops.dense_backward_dx(b["dz"][i][sl], self._w(i), b["a"][i][sl], self.layer_params[i - 1]["activation"],
+                                  out=b["dz"][i - 1][sl])
+        if not need_input_grad:
+            return None
+        ops.dense_backward_dx(b["dz"][0][sl], self._w(0), b["a"][0][sl], self.input_activation, out=b["dx"][sl])
+        return b["dx"][sl]
+
+    def step(self, lr: float, rows: Optional[int] = None) -> None:
+        """dW = A^T.dZ over the first ``rows`` buffered rows with the SGD update fused into the
+        GEMM epilogue: W -= lr*dW, b -= lr*db, bf16 shadow refreshed."""
+        rows = self._rows if rows is None else rows
+        b = self._bufs
+        for i, p in enumerate(self.layer_params):
+            ops.dense_backward_dw_sgd(b["a"][i][:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
+                                      w_shadow=self._shadow[i], workspace=self._ws)
+
+    def gradients(self, rows: Optional[int] = None):
+        """[(dW, db)] per local layer from the buffered activations/gradients (no update)."""
+        rows = self._rows if rows is None else rows
+        b = self._bufs
+        return [ops.dense_backward_dw(b["a"][i][:rows], b["dz"][i][:rows], workspace=self._ws)
+                for i in range(len(self.layer_params))]
+
+    def zero_loss(self) -> None:
+        self._bufs["loss"].zero_()
+
+    # ------------------------------------------------------------------ export
+    def export_params(self) -> List[Dict[str, Any]]:
+        """float64 numpy copies in the oracle/reference layout (for JSON export and parity)."""
+        return [{"weights": p["weights"].double().cpu().numpy(), "biases": p["biases"].double().cpu().numpy(),
+                 "activation": p["activation"]} for p in self.layer_params]

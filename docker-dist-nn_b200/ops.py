@@ -1,0 +1,165 @@
+"""Thin torch-tensor wrappers over the C ABI (include/ddnn.h).
+
+torch is used for device memory and the current stream only; every computation below is
+one call into libddnn.so.  Tensors must be CUDA, contiguous and of the dtype stated.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import ACT_LINEAR, ACT_SOFTMAX, BF16, F32, check, lib
+
+_DT = {torch.float32: F32, torch.bfloat16: BF16}
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _req(t: torch.Tensor, dtype=None, name="tensor") -> None:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must live on a CUDA device: libddnn has no CPU path")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+def dense_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, act, out: Optional[torch.Tensor] = None,
+                  out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+    """act(x @ w + bias).  x (B,K), w (K,N) share a dtype (fp32/bf16); bias fp32."""
+    _req(x, name="x"); _req(w, x.dtype, "w"); _req(bias, torch.float32, "bias")
+    b, k = x.shape
+    k2, n = w.shape
+    if k != k2 or bias.numel() != n:
+        raise ValueError(f"expected input dim {k2}, got {k}")
+    act_id = act if isinstance(act, int) else _lib.activation_id(act)
+    if out is None:
+        od = out_dtype or (torch.float32 if act_id == ACT_SOFTMAX else x.dtype)
+        out = torch.empty((b, n), dtype=od, device=x.device)
+    _req(out, name="out")
+    with torch.cuda.device(x.device):
+        check(lib.ddnn_dense_forward(_p(x), _p(w), _p(bias), _p(out), b, k, n, act_id, _DT[x.dtype], _DT[out.dtype],
+                                     _stream(x)))
+    return out
+
+
+def softmax_rows(z: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _req(z, torch.float32, "z")
+    out = torch.empty_like(z) if out is None else out
+    _req(out, torch.float32, "out")
+    with torch.cuda.device(z.device):
+        check(lib.ddnn_softmax_rows(_p(z), _p(out), z.shape[0], z.shape[1], _stream(z)))
+    return out
+
+
+def activate(v: torch.Tensor, act, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    _req(v, torch.float32, "values")
+    if v.dim() != 2:
+        raise ValueError("values must be 2-D (rows, features)")
+    out = torch.empty_like(v) if out is None else out
+    act_id = act if isinstance(act, int) else _lib.activation_id(act)
+    with torch.cuda.device(v.device):
+        check(lib.ddnn_activate(_p(v), _p(out), v.shape[0], v.shape[1], act_id, _stream(v)))
+    return out
+
+
+def softmax_ce(z: torch.Tensor, labels: torch.Tensor, dz: torch.Tensor, row_loss: torch.Tensor, loss: torch.Tensor,
+               inv_denom: float, p: Optional[torch.Tensor] = None, accumulate: bool = False) -> None:
+    """dz = (softmax(z) - onehot(labels)) * inv_denom ; loss (+)= inv_denom * sum(-log p[y])."""
+    _req(z, torch.float32, "z"); _req(labels, torch.int32, "labels"); _req(dz, name="dz")
+    _req(row_loss, torch.float32, "row_loss"); _req(loss, torch.float32, "loss")
+    if p is not None:
+        _req(p, torch.float32, "p")
+    b, n = z.shape
+    if labels.numel() != b or dz.shape != z.shape or row_loss.numel() < b:
+        raise ValueError("softmax_ce: shape mismatch")
+    with torch.cuda.device(z.device):
+        check(lib.ddnn_softmax_ce(_p(z), _p(labels), _p(p), _p(dz), _p(row_loss), _p(loss), b, n, float(inv_denom),
+                                  _DT[dz.dtype], 1 if accumulate else 0, _stream(z)))
+
+
+def dense_backward_dx(dz: torch.Tensor, w: torch.Tensor, a_prev: Optional[torch.Tensor], act_prev,
+                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(dz @ w.T) * f'(a_prev) with f' of the previous layer's activation."""
+    _req(dz, name="dz"); _req(w, dz.dtype, "w")
+    b, n = dz.shape
+    k, n2 = w.shape
+    if n != n2:
+        raise ValueError(f"expected gradient width {n2}, got {n}")
+    act_id = act_prev if isinstance(act_prev, int) else _lib.activation_id(act_prev)
+    if a_prev is not None:
+        _req(a_prev, dz.dtype, "a_prev")
+    if out is None:
+        out = torch.empty((b, k), dtype=dz.dtype, device=dz.device)
+    _req(out, dz.dtype, "out")
+    with torch.cuda.device(dz.device):
+        check(lib.ddnn_dense_backward_dx(_p(dz), _p(w), _p(a_prev if act_id != ACT_LINEAR else None), _p(out), b, k,
+                                         n, act_id, _DT[dz.dtype], _stream(dz)))
+    return out
+
+
+def dw_workspace_bytes(b: int, k: int, n: int, dtype: torch.dtype) -> int:
+    return int(lib.ddnn_dw_workspace_bytes(b, k, n, _DT[dtype]))
+
+
+def dense_backward_dw(x: torch.Tensor, dz: torch.Tensor, workspace: Optional[torch.Tensor] = None
+                      ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Gradients only: (x.T @ dz, column sums of dz), both fp32."""
+    _req(x, name="x"); _req(dz, x.dtype, "dz")
+    b, k = x.shape
+    n = dz.shape[1]
+    dw = torch.empty((k, n), dtype=torch.float32, device=x.device)
+    db = torch.empty((n,), dtype=torch.float32, device=x.device)
+    ws = _workspace(workspace, b, k, n, x)
+    with torch.cuda.device(x.device):
+        check(lib.ddnn_dense_backward_dw_sgd(_p(x), _p(dz), None, None, None, _p(dw), _p(db), 0.0, 0, b, k, n,
+                                             _DT[x.dtype], _p(ws), ws.numel(), _stream(x)))
+    return dw, db
+
+
+def dense_backward_dw_sgd(x: torch.Tensor, dz: torch.Tensor, w_master: torch.Tensor, bias: torch.Tensor, lr: float,
+                          w_shadow: Optional[torch.Tensor] = None, workspace: Optional[torch.Tensor] = None) -> None:
+    """Fused update: w_master -= lr * x.T @ dz ; bias -= lr * colsum(dz) ; shadow = bf16(w_master)."""
+    _req(x, name="x"); _req(dz, x.dtype, "dz"); _req(w_master, torch.float32, "w_master")
+    _req(bias, torch.float32, "bias")
+    if w_shadow is not None:
+        _req(w_shadow, torch.bfloat16, "w_shadow")
+    b, k = x.shape
+    n = dz.shape[1]
+    if tuple(w_master.shape) != (k, n) or dz.shape[0] != b:
+        raise ValueError("dense_backward_dw_sgd: shape mismatch")
+    ws = _workspace(workspace, b, k, n, x)
+    with torch.cuda.device(x.device):
+        check(lib.ddnn_dense_backward_dw_sgd(_p(x), _p(dz), _p(w_master), _p(w_shadow), _p(bias), None, None, float(lr),
+                                             1, b, k, n, _DT[x.dtype], _p(ws), ws.numel(), _stream(x)))
+
+
+def _workspace(ws: Optional[torch.Tensor], b: int, k: int, n: int, like: torch.Tensor) -> torch.Tensor:
+    need = dw_workspace_bytes(b, k, n, like.dtype)
+    if ws is None or ws.numel() < need:
+        ws = torch.empty((max(need, 256),), dtype=torch.uint8, device=like.device)
+    return ws
+
+
+def cast(t: torch.Tensor, dtype: torch.dtype, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 <-> bf16 through the library's cast kernels."""
+    _req(t, name="t")
+    if out is None:
+        out = torch.empty(t.shape, dtype=dtype, device=t.device)
+    _req(out, dtype, "out")
+    with torch.cuda.device(t.device):
+        if t.dtype == torch.float32 and dtype == torch.bfloat16:
+            check(lib.ddnn_cast_f32_to_bf16(_p(t), _p(out), t.numel(), _stream(t)))
+        elif t.dtype == torch.bfloat16 and dtype == torch.float32:
+            check(lib.ddnn_cast_bf16_to_f32(_p(t), _p(out), t.numel(), _stream(t)))
+        else:
+            raise TypeError(f"cast {t.dtype} -> {dtype} not supported")
+    return out

@@ -1,0 +1,131 @@
+/*
+ * ddnn.h -- C ABI of libddnn.so: the docker-dist-nn layer hot path on B200 (sm_100a).
+ *
+ * The reference has no FFI: its hot path is three Python methods of one class,
+ * /root/reference/src/grpc_node.py:16-97 (Layer.__init__ / activate / process_matrix),
+ * which call numpy.  Each entry point below names the numpy call site it replaces.
+ * Backward, softmax-CE and SGD have no reference counterpart;
+ * they are specified by BASELINE.json's north_star and derived from the forward.
+ *
+ * Conventions
+ *  - every pointer is a DEVICE pointer owned by the caller (incl. workspace); the
+ *    library allocates no device memory and keeps no state besides a mutex-guarded
+ *    cache of TMA descriptors keyed by (pointer, shape);
+ *  - matrices are row-major, (batch, features); weights are (K = in, N = out) like
+ *    grpc_node.py:51 (`np.array([...]).T`);
+ *  - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, nothing
+ *    synchronises;
+ *  - return value: 0 = ok, otherwise a ddnn_status; ddnn_last_error() gives the text
+ *    for the calling thread.  Nothing throws across the ABI.
+ *  - B == 0 is legal everywhere and does nothing (grpc_node.py:108-111 returns an
+ *    empty Matrix for an empty request).
+ */
+#ifndef DDNN_H_
+#define DDNN_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  DDNN_OK = 0,
+  DDNN_ERR_DIM = 1,          /* shape mismatch -> Python raises ValueError (grpc_node.py:83-84) */
+  DDNN_ERR_ACTIVATION = 2,   /* activation not supported by this entry point */
+  DDNN_ERR_CUDA = 3,         /* a CUDA call failed; text in ddnn_last_error() */
+  DDNN_ERR_ARG = 4,          /* null / misaligned pointer, bad enum */
+  DDNN_ERR_WORKSPACE = 5,    /* workspace smaller than ddnn_*_workspace_bytes() */
+  DDNN_ERR_UNSUPPORTED = 6   /* dtype/shape combination has no kernel */
+} ddnn_status;
+
+/* grpc_node.py:62-73.  Any string that is not relu/sigmoid/softmax is the identity. */
+typedef enum { DDNN_ACT_LINEAR = 0, DDNN_ACT_RELU = 1, DDNN_ACT_SIGMOID = 2, DDNN_ACT_SOFTMAX = 3 } ddnn_act;
+
+/* Element type of activations / weight operands.  Accumulation is always fp32. */
+typedef enum { DDNN_F32 = 0, DDNN_BF16 = 1 } ddnn_dtype;
+
+/* Which GEMM engine to use.  AUTO: tcgen05 when dtype is bf16 and the shape meets the
+ * TMA alignment rules (feature widths multiples of 8), else the SIMT kernels. */
+typedef enum { DDNN_ENGINE_AUTO = 0, DDNN_ENGINE_SIMT = 1, DDNN_ENGINE_TCGEN05 = 2 } ddnn_engine;
+
+int ddnn_version(void);
+const char* ddnn_last_error(void);
+
+/* Maps an activation string the way Layer.activate does (grpc_node.py:62-73). */
+int ddnn_activation_from_name(const char* name);
+
+/* Force an engine for subsequent calls of this process (tests / profiling). */
+int ddnn_set_engine(int engine);
+
+/*
+ * A[B,N] = act(X[B,K] . W[K,N] + bias[N])
+ * Replaces `np.dot(current_matrix, params["weights"]) + params["biases"]`
+ * (grpc_node.py:87) and `self.activate(raw_output, ...)` (grpc_node.py:90, :62-73).
+ * X, W have element type `dtype`; A has `out_dtype`; bias is fp32.
+ * act == SOFTMAX applies the row softmax of grpc_node.py:68-71 in a second launch.
+ */
+int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A,
+                       int64_t B, int64_t K, int64_t N,
+                       int act, int dtype, int out_dtype, void* stream);
+
+/* P[B,N] = row softmax of Z (grpc_node.py:68-71); in place allowed.  fp32 in/out. */
+int ddnn_softmax_rows(const float* Z, float* P, int64_t B, int64_t N, void* stream);
+
+/* Elementwise activation, replaces Layer.activate for relu/sigmoid/linear/softmax on an
+ * arbitrary fp32 matrix (grpc_node.py:62-73).  In place allowed. */
+int ddnn_activate(const float* V, float* out, int64_t B, int64_t N, int act, void* stream);
+
+/*
+ * Softmax cross-entropy at the output node.  No reference counterpart; semantics of
+ * nn.CrossEntropyLoss(mean) at /root/reference/scripts/generate_mnist_pytorch.py:37.
+ *   p = softmax(Z);  row_loss[i] = -log p[i,y_i];  dZ = (p - onehot(y)) * inv_denom
+ *   *loss (+)= inv_denom * sum_i row_loss[i]      (accumulate != 0 adds to *loss)
+ * Z fp32 [B,N]; labels int32 [B]; P (fp32, nullable) receives the probabilities;
+ * dZ has element type dz_dtype; row_loss is fp32 [B] scratch/output owned by the caller;
+ * loss is one fp32 on the device.
+ */
+int ddnn_softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ,
+                    float* row_loss, float* loss, int64_t B, int64_t N,
+                    float inv_denom, int dz_dtype, int accumulate, void* stream);
+
+/*
+ * dZprev[B,K] = (dZ[B,N] . W[K,N]^T) * f'(Aprev[B,K])
+ * f' from the activation of the PREVIOUS layer, evaluated on its stored output:
+ * relu -> 1[A>0], sigmoid -> A(1-A), linear -> 1.  SOFTMAX is rejected (hidden softmax
+ * needs the row Jacobian; DDNN_ERR_ACTIVATION).  No reference counterpart.
+ */
+int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev,
+                           int64_t B, int64_t K, int64_t N,
+                           int act_prev, int dtype, void* stream);
+
+/*
+ * dW[K,N] = X[B,K]^T . dZ[B,N];  db[N] = column sums of dZ;  then either
+ *   apply != 0 :  W_master -= lr*dW ; bias -= lr*db ; W_shadow = bf16(W_master) if given
+ *   apply == 0 :  dW_out = dW, db_out = db            (fp32; for gradient checks)
+ * W_master is fp32 [K,N] (in f32 mode it IS the weight the forward reads); W_shadow is
+ * the bf16 copy the bf16 forward/dX read (nullable).  Split-K partial sums go through
+ * `workspace` (fp32, >= ddnn_dw_workspace_bytes) and are reduced in a fixed order, so
+ * results are run-to-run deterministic.  No reference counterpart.
+ */
+int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ,
+                               float* W_master, void* W_shadow, float* bias,
+                               float* dW_out, float* db_out,
+                               float lr, int apply,
+                               int64_t B, int64_t K, int64_t N, int dtype,
+                               void* workspace, size_t workspace_bytes, void* stream);
+
+size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype);
+
+/* out[i] = bf16(in[i]) / fp32(in[i]) converters for staging host-provided fp32 data. */
+int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
+int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
+
+/* Count of kernels this library has launched in this process (bench.py gpu_launches). */
+int64_t ddnn_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDNN_H_ */

@@ -1,0 +1,28 @@
+import numpy as np
+import torch
+
+
+def rel_err(got, ref) -> float:
+    """max |got - ref| / max |ref|  (normalised max error; scale-free, robust near zero)."""
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    if ref.size == 0:
+        return 0.0
+    return float(np.max(np.abs(got - ref)) / (np.max(np.abs(ref)) + 1e-300))
+
+
+def to_dev(a, dtype=torch.float32, device="cuda"):
+    return torch.as_tensor(np.ascontiguousarray(a), dtype=dtype).to(device).contiguous()
+
+
+def to_np(t):
+    return t.detach().double().cpu().numpy()
+
+
+# north_star: fp32 path within 1e-5 relative of the float64 reference
+F32_TOL = 1e-5
+# bf16 operands (8-bit mantissa, eps = 2^-8) with fp32 accumulation: activations within 2e-2 of
+# the float64 oracle (normalised max error), weight gradients within 3e-2
+BF16_ACT_TOL = 2e-2
+BF16_GRAD_TOL = 3e-2

@@ -1,0 +1,50 @@
+"""The C-ABI library loads on a machine without a GPU and exports every symbol that
+include/ddnn.h declares (no compute calls here)."""
+import ctypes
+import os
+import re
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(REPO, "include", "ddnn.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(ddnn_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported():
+    from ddnn_b200 import _lib
+    names = _declared()
+    assert len(names) >= 14
+    raw = ctypes.CDLL(str(_lib.LIB_PATH))
+    for n in names:
+        assert hasattr(raw, n), f"{n} declared in include/ddnn.h but not exported"
+    # and the Python binding covers exactly the declared set
+    assert sorted(_lib.SYMBOLS) == names
+
+
+def test_host_only_entry_points():
+    from ddnn_b200 import _lib
+    assert _lib.lib.ddnn_version() >= 100
+    assert _lib.activation_id("relu") == _lib.ACT_RELU
+    assert _lib.activation_id("sigmoid") == _lib.ACT_SIGMOID
+    assert _lib.activation_id("softmax") == _lib.ACT_SOFTMAX
+    for other in ("linear", "unknown", "tanh", "", None):  # grpc_node.py:72-73
+        assert _lib.activation_id(other) == _lib.ACT_LINEAR
+    assert _lib.lib.ddnn_dw_workspace_bytes(4096, 784, 128, _lib.F32) > 0
+    assert _lib.lib.ddnn_dw_workspace_bytes(0, 784, 128, _lib.F32) == 0
+    # argument errors are reported through the status code + ddnn_last_error, never thrown
+    rc = _lib.lib.ddnn_dense_forward(None, None, None, None, 4, 0, 3, 0, 0, 0, None)
+    assert rc == _lib.ERR_DIM and "bad dimensions" in _lib.last_error()
+    rc = _lib.lib.ddnn_set_engine(9)
+    assert rc == _lib.ERR_ARG
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(REPO, "docker-dist-nn_b200")
+    for root, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                src = open(os.path.join(root, f)).read()
+                assert "import oracle" not in src and "from oracle" not in src, f

@@ -1,0 +1,167 @@
+"""Parity of every C-ABI entry point with the float64 oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from gpu_util import BF16_ACT_TOL, BF16_GRAD_TOL, F32_TOL, rel_err, to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+ACTS = ["relu", "sigmoid", "linear", "softmax"]
+# (B, K, N): MNIST layers, ragged / non-multiple-of-tile, N = 10, B = 1, wide-ish
+SHAPES = [(64, 784, 128), (33, 128, 64), (50, 64, 10), (1, 7, 3), (257, 100, 130), (128, 256, 256), (5, 3, 1)]
+
+
+def _data(b, k, n, seed=0):
+    rng = np.random.default_rng(seed)
+    x = rng.random((b, k)) - 0.25
+    w = rng.standard_normal((k, n)) / np.sqrt(k)
+    bias = rng.standard_normal(n) * 0.1
+    return x, w, bias
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("act", ACTS)
+def test_forward_f32(cuda_device, shape, act):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    x, w, bias = _data(b, k, n)
+    ref = oracle.activate(np.dot(x, w) + bias, act)
+    got = ops.dense_forward(to_dev(x), to_dev(w), to_dev(bias), act)
+    assert rel_err(to_np(got), ref) < F32_TOL
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("act_prev", ["relu", "sigmoid", "linear"])
+def test_backward_dx_f32(cuda_device, shape, act_prev):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    rng = np.random.default_rng(1)
+    dz = rng.standard_normal((b, n))
+    w = rng.standard_normal((k, n)) / np.sqrt(n)
+    zprev = rng.standard_normal((b, k))
+    aprev = oracle.activate(zprev, act_prev)
+    ref = oracle.ddnn_oracle._act_backward(np.dot(dz, w.T), aprev, zprev, act_prev)
+    got = ops.dense_backward_dx(to_dev(dz), to_dev(w), to_dev(aprev), act_prev)
+    assert rel_err(to_np(got), ref) < F32_TOL
+
+
+def test_backward_dx_rejects_hidden_softmax(cuda_device):
+    from ddnn_b200 import _lib, ops
+    t = torch.zeros((4, 4), device="cuda")
+    with pytest.raises(_lib.DdnnError) as e:
+        ops.dense_backward_dx(t, t, t, "softmax")
+    assert e.value.status == _lib.ERR_ACTIVATION
+
+
+@pytest.mark.parametrize("shape", SHAPES + [(4096, 784, 128), (1000, 10, 10)])
+def test_backward_dw_f32(cuda_device, shape):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    rng = np.random.default_rng(2)
+    x = rng.random((b, k))
+    dz = rng.standard_normal((b, n)) / b
+    dw, db = ops.dense_backward_dw(to_dev(x), to_dev(dz))
+    assert rel_err(to_np(dw), np.dot(x.T, dz)) < F32_TOL
+    assert rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+
+
+@pytest.mark.parametrize("shape", [(64, 784, 128), (50, 64, 10), (257, 100, 130)])
+def test_dw_sgd_fused_update_f32(cuda_device, shape):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    rng = np.random.default_rng(3)
+    x, dz = rng.random((b, k)), rng.standard_normal((b, n)) / b
+    w, bias = rng.standard_normal((k, n)), rng.standard_normal(n)
+    wd, bd = to_dev(w), to_dev(bias)
+    ops.dense_backward_dw_sgd(to_dev(x), to_dev(dz), wd, bd, 0.1)
+    assert rel_err(to_np(wd), w - 0.1 * np.dot(x.T, dz)) < F32_TOL
+    assert rel_err(to_np(bd), bias - 0.1 * dz.sum(axis=0)) < F32_TOL
+
+
+def test_dw_is_run_to_run_deterministic(cuda_device):
+    from ddnn_b200 import ops
+    rng = np.random.default_rng(4)
+    x, dz = to_dev(rng.random((4096, 784))), to_dev(rng.standard_normal((4096, 128)))
+    a, _ = ops.dense_backward_dw(x, dz)
+    b, _ = ops.dense_backward_dw(x, dz)
+    assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("bn", [(64, 10), (7, 2), (33, 100), (16, 1000), (9, 1024), (5, 1030), (4, 8192), (3, 4099)])
+def test_softmax_ce(cuda_device, bn):
+    from ddnn_b200 import ops
+    b, n = bn
+    rng = np.random.default_rng(5)
+    z = rng.standard_normal((b, n)) * 3
+    y = rng.integers(0, n, size=b)
+    loss, p, dz = oracle.softmax_ce(z, y, denom=b * 2)
+    zd = to_dev(z)
+    dzd = torch.empty_like(zd)
+    pd = torch.empty_like(zd)
+    rl = torch.empty((b,), device="cuda")
+    ls = torch.zeros((1,), device="cuda")
+    ops.softmax_ce(zd, to_dev(y, torch.int32), dzd, rl, ls, 1.0 / (b * 2), p=pd)
+    assert rel_err(to_np(pd), p) < F32_TOL
+    assert rel_err(to_np(dzd), dz) < F32_TOL
+    assert abs(ls.item() - loss) < F32_TOL * abs(loss) + 1e-7
+    # accumulate adds
+    ops.softmax_ce(zd, to_dev(y, torch.int32), dzd, rl, ls, 1.0 / (b * 2), accumulate=True)
+    assert abs(ls.item() - 2 * loss) < 2 * F32_TOL * abs(loss) + 1e-6
+    # softmax rows (grpc_node.py:68-71), in place
+    ops.softmax_rows(zd, out=zd)
+    assert rel_err(to_np(zd), oracle.activate(z, "softmax")) < F32_TOL
+
+
+def test_activate_matches_reference_grid(cuda_device, golden_small):
+    from ddnn_b200 import ops
+    a = golden_small["activations"]
+    grid = np.array(a["grid"])
+    for func in ("relu", "sigmoid", "softmax", "unknown"):
+        got = to_np(ops.activate(to_dev(grid), func))
+        np.testing.assert_allclose(got, np.array(a["outputs"][func]), rtol=1e-5, atol=1e-30)
+
+
+def test_empty_batch_is_a_no_op(cuda_device):
+    from ddnn_b200 import ops
+    x = torch.empty((0, 8), device="cuda")
+    w = torch.zeros((8, 4), device="cuda")
+    out = ops.dense_forward(x, w, torch.zeros(4, device="cuda"), "relu")
+    assert out.shape == (0, 4)
+
+
+def test_cast_roundtrip(cuda_device):
+    from ddnn_b200 import ops
+    t = torch.randn(1003, device="cuda")
+    b = ops.cast(t, torch.bfloat16)
+    assert torch.equal(b, t.to(torch.bfloat16))
+    assert torch.equal(ops.cast(b, torch.float32), b.float())
+
+
+# ---- bf16 operands on the SIMT engine (narrow / misaligned layers of a bf16 model) -------------
+
+@pytest.mark.parametrize("shape", [(64, 784, 128), (50, 64, 10), (257, 100, 130)])
+def test_bf16_simt_engine(cuda_device, shape):
+    from ddnn_b200 import _lib, ops
+    b, k, n = shape
+    x, w, bias = _data(b, k, n, seed=6)
+    rng = np.random.default_rng(7)
+    dz = rng.standard_normal((b, n)) / b
+    _lib.set_engine(_lib.ENGINE_SIMT)
+    try:
+        xb, wb, dzb = (to_dev(t, torch.bfloat16) for t in (x, w, dz))
+        # compare against the oracle evaluated on the bf16-rounded operands: isolates kernel error
+        xr, wr, dzr = (to_np(t) for t in (xb, wb, dzb))
+        got = ops.dense_forward(xb, wb, to_dev(bias), "relu", out_dtype=torch.float32)
+        assert rel_err(to_np(got), oracle.activate(np.dot(xr, wr) + bias, "relu")) < F32_TOL
+        got = ops.dense_forward(xb, wb, to_dev(bias), "relu")
+        assert rel_err(to_np(got), oracle.activate(np.dot(x, w) + bias, "relu")) < BF16_ACT_TOL
+        dw, db = ops.dense_backward_dw(xb, dzb)
+        assert rel_err(to_np(dw), np.dot(xr.T, dzr)) < F32_TOL
+        assert rel_err(to_np(dw), np.dot(x.T, dz)) < BF16_GRAD_TOL
+        assert rel_err(to_np(db), dzr.sum(axis=0)) < F32_TOL
+        dx = ops.dense_backward_dx(dzb, wb, None, "linear")
+        assert rel_err(to_np(dx), np.dot(dz, w.T)) < BF16_ACT_TOL
+    finally:
+        _lib.set_engine(_lib.ENGINE_AUTO)

@@ -1,0 +1,211 @@
+"""The reference-facing API (`Layer`, `Trainer`) on the GPU: forward against the reference's
+golden vectors, training against the float64 oracle's N-step weight trajectory."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from ddnn_b200.config import make_params, synthetic_batch
+from gpu_util import BF16_ACT_TOL, F32_TOL, rel_err, to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+
+def _env_layer(neurons_config, dim, **extra):
+    from ddnn_b200 import Layer
+    env = {"CONTAINER_NAME": "golden", "EXPECTED_INPUT_DIM": str(dim), "NEURONS_CONFIG": json.dumps(neurons_config),
+           "NEXT_NODES": "[]", **extra}
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    os.environ.pop("NEURONS_FILE_CONFIG", None)
+    try:
+        return Layer()
+    finally:
+        for k, v in old.items():
+            os.environ.pop(k, None) if v is None else os.environ.__setitem__(k, v)
+
+
+def test_kat_through_env_contract(cuda_device, golden_small):
+    k = golden_small["kat"]
+    L = _env_layer(k["neurons_config"], k["expected_input_dim"])
+    assert L.container_name == "golden" and L.expected_input_dim == 2 and L.next_nodes == []
+    assert tuple(L.layer_params[0]["weights"].shape) == (2, 3)  # (in, out), grpc_node.py:51
+    out = L.process_matrix(np.array(k["input"]))
+    assert out.dtype == np.float64
+    np.testing.assert_allclose(out, np.array(k["output"]), rtol=F32_TOL)
+
+
+def test_file_config_and_missing_config(cuda_device, golden_small, tmp_path):
+    from ddnn_b200 import Layer
+    k = golden_small["kat"]
+    f = tmp_path / "n.json"
+    f.write_text(json.dumps(k["neurons_config"]))
+    old = {v: os.environ.pop(v, None) for v in ("NEURONS_CONFIG", "NEURONS_FILE_CONFIG")}
+    try:
+        os.environ["NEURONS_FILE_CONFIG"] = str(f)
+        os.environ["EXPECTED_INPUT_DIM"] = "2"
+        L = Layer()
+        np.testing.assert_allclose(L.process_matrix(np.array(k["input"])), np.array(k["output"]), rtol=F32_TOL)
+        os.environ["NEURONS_FILE_CONFIG"] = str(tmp_path / "absent.json")
+        with pytest.raises(SystemExit) as e:   # grpc_node.py:32-34
+            Layer()
+        assert e.value.code == 1
+        os.environ.pop("NEURONS_FILE_CONFIG")
+        with pytest.raises(SystemExit):        # grpc_node.py:38-41
+            Layer()
+    finally:
+        os.environ.pop("EXPECTED_INPUT_DIM", None)
+        for k_, v in old.items():
+            if v is not None:
+                os.environ[k_] = v
+
+
+def test_small_net_prefixes_and_errors(cuda_device, golden_small):
+    s = golden_small["small_net"]
+    x = np.array(s["input"])
+    for upto, expect in s["prefix_outputs"].items():
+        nc = {f"layer_{i + 1}": s["config"]["layers"][i]["neurons"] for i in range(int(upto))}
+        out = _env_layer(nc, 5).process_matrix(x)
+        assert rel_err(out, np.array(expect)) < F32_TOL, f"prefix {upto}"
+    nc = {f"layer_{i + 1}": s["config"]["layers"][i]["neurons"] for i in range(4)}
+    L = _env_layer(nc, 5)
+    with pytest.raises(ValueError) as e:
+        L.process_matrix(np.zeros((2, 3)))
+    assert str(e.value) == "(golden) Layer 1: expected input dim 5, got 3"  # grpc_node.py:84 text
+    assert L.process_matrix(np.zeros((0, 5))).shape == (0, 3)           # empty in -> empty out
+    # CUDA tensor in -> CUDA tensor out
+    out = L.process_matrix(to_dev(x))
+    assert out.is_cuda and rel_err(to_np(out), np.array(s["prefix_outputs"]["4"])) < F32_TOL
+    # activate(): reference semantics incl. unknown -> identity
+    a = golden_small["activations"]
+    for func in ("relu", "sigmoid", "softmax", "tanh"):
+        np.testing.assert_allclose(L.activate(np.array(a["grid"]), func), np.array(a["outputs"][func]), rtol=1e-5,
+                                   atol=1e-30)
+
+
+def test_mnist_forward_golden(cuda_device, golden_mnist):
+    from ddnn_b200 import Layer
+    for tag, dims in (("mnist_128_64", [784, 128, 64, 10]), ("mnist_32_16", [784, 32, 16, 10])):
+        params = make_params(dims, ["relu", "relu", "softmax"], seed=1)
+        L = Layer.from_params(params, 784)
+        out = L.process_matrix(golden_mnist[f"{tag}_x"])
+        assert rel_err(out, golden_mnist[f"{tag}_out"]) < F32_TOL
+        assert np.array_equal(out.argmax(axis=1), golden_mnist[f"{tag}_out"].argmax(axis=1))
+        Lb = Layer.from_params(params, 784, dtype="bf16")
+        assert rel_err(Lb.process_matrix(golden_mnist[f"{tag}_x"]), golden_mnist[f"{tag}_out"]) < BF16_ACT_TOL
+
+
+@pytest.mark.parametrize("dims,acts", [([784, 128, 64, 10], ["relu", "relu", "softmax"]),
+                                        ([784, 32, 16, 10], ["relu", "relu", "softmax"]),
+                                        ([20, 17, 9, 5], ["sigmoid", "relu", "linear"])])
+def test_gradients_match_oracle(cuda_device, dims, acts):
+    from ddnn_b200 import Trainer
+    params = make_params(dims, acts, seed=1)
+    x, y = synthetic_batch(96, dims[0], dims[-1], seed=0)
+    a, zs = oracle.forward_all(params, x)
+    loss, dws, dbs, _ = oracle.backward(params, a, zs, y)
+    t = Trainer(params)
+    L = t.layer
+    L.begin_batch(96)
+    L.forward_train(to_dev(x), 0)
+    gl = L.loss_and_grad(to_dev(y, torch.int32), 0)
+    L.backward(0, 96, need_input_grad=False)
+    assert abs(gl.item() - loss) < F32_TOL * loss
+    for (dw, db), rw, rb in zip(L.gradients(), dws, dbs):
+        assert rel_err(to_np(dw), rw) < F32_TOL
+        assert rel_err(to_np(db), rb) < F32_TOL
+
+
+def test_n_step_weight_trajectory_f32(cuda_device):
+    """Sequential unshuffled batches with a ragged tail (run_grpc_inference.py:198-205 order),
+    20 SGD steps: losses and post-step weights track the float64 oracle within 1e-5."""
+    from ddnn_b200 import Trainer
+    from ddnn_b200.config import batch_slices
+    dims, acts = [784, 128, 64, 10], ["relu", "relu", "softmax"]
+    params = make_params(dims, acts, seed=1)
+    ref = [dict(p) for p in make_params(dims, acts, seed=1)]
+    x, y = synthetic_batch(1000, 784, 10, seed=0)
+    t = Trainer(params)
+    got_losses = t.fit((x, y), epochs=2, batch_size=96, lr=0.05)
+    ref_losses = []
+    for _ in range(2):
+        for (a, b) in batch_slices(1000, 96):
+            ref_losses.append(oracle.train_step(ref, x[a:b], y[a:b], 0.05))
+    assert len(got_losses) == len(ref_losses) == 22
+    np.testing.assert_allclose(got_losses, ref_losses, rtol=F32_TOL)
+    for g, r in zip(t.export_params(), ref):
+        assert rel_err(g["weights"], r["weights"]) < F32_TOL
+        assert rel_err(g["biases"], r["biases"]) < F32_TOL
+
+
+def test_cuda_graph_step_equals_eager(cuda_device):
+    from ddnn_b200 import Trainer
+    dims, acts = [784, 32, 16, 10], ["relu", "relu", "softmax"]
+    x, y = synthetic_batch(256, 784, 10, seed=3)
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    eager = Trainer(make_params(dims, acts, seed=1))
+    graph = Trainer(make_params(dims, acts, seed=1))
+    graph.capture(256, lr=0.05)
+    sx, sy = graph.static_inputs
+    sx.copy_(xd); sy.copy_(yd)
+    for _ in range(3):
+        le = eager.train_step(xd, yd, 0.05).item()
+        lg = graph.replay().item()
+        assert le == lg
+    for a, b in zip(eager.export_params(), graph.export_params()):
+        assert np.array_equal(a["weights"], b["weights"])
+    # host entry point goes through the same graph
+    l = graph.train_step_host(torch.as_tensor(x, dtype=torch.float32).pin_memory(),
+                              torch.as_tensor(y, dtype=torch.int32).pin_memory())
+    assert np.isfinite(l)
+
+
+def test_bf16_training_tracks_loss_curve(cuda_device):
+    """bf16 tensor-core path: looser bound, matching loss curve (north_star)."""
+    from ddnn_b200 import Trainer
+    dims, acts = [256, 256, 128, 64], ["relu", "relu", "softmax"]
+    params = make_params(dims, acts, seed=2)
+    ref = [dict(p) for p in make_params(dims, acts, seed=2)]
+    x, y = synthetic_batch(512, 256, 64, seed=1)
+    t = Trainer(params, dtype="bf16")
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    for step in range(10):
+        lg = t.train_step(xd, yd, 0.1).item()
+        lr_ = oracle.train_step(ref, x, y, 0.1)
+        assert abs(lg - lr_) < 2e-2 * lr_, (step, lg, lr_)
+    for g, r in zip(t.export_params(), ref):
+        assert rel_err(g["weights"], r["weights"]) < BF16_ACT_TOL
+    # the bf16 shadow is exactly the rounded master
+    for p, sh in zip(t.layer.layer_params, t.layer._shadow):
+        assert torch.equal(sh, p["weights"].to(torch.bfloat16))
+
+
+def test_two_stage_chain_equals_single_node(cuda_device):
+    """[2, 1] split on one device: stage 2's dX applies stage 1's activation derivative; the
+    deferred full-batch dW step over 3 micro-batches equals the single-node step."""
+    from ddnn_b200 import Layer, Trainer
+    dims, acts = [64, 48, 40, 10], ["relu", "sigmoid", "softmax"]
+    x, y = synthetic_batch(90, 64, 10, seed=5)
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    single = Trainer(make_params(dims, acts, seed=4))
+    single.train_step(xd, yd, 0.1)
+    p = make_params(dims, acts, seed=4)
+    s0 = Layer.from_params(p[:2], 64, is_output=False)
+    s1 = Layer.from_params(p[2:], 40, is_output=True, input_activation="sigmoid")
+    s0.begin_batch(90); s1.begin_batch(90)
+    for r0 in (0, 30, 60):
+        out = s0.forward_train(xd[r0:r0 + 30], r0)
+        s1.forward_train(out, r0)
+    for i, r0 in enumerate((0, 30, 60)):
+        s1.loss_and_grad(yd[r0:r0 + 30], r0, denom=90, accumulate=i > 0)
+        dx = s1.backward(r0, 30)
+        s0.grad_buffer(r0, 30).copy_(dx)
+        s0.backward(r0, 30, need_input_grad=False)
+    s0.step(0.1); s1.step(0.1)
+    chained = s0.export_params() + s1.export_params()
+    for a, b in zip(single.export_params(), chained):
+        assert rel_err(b["weights"], a["weights"]) < 1e-6
+        assert rel_err(b["biases"], a["biases"]) < 1e-6

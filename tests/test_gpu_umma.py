@@ -1,0 +1,134 @@
+"""The tcgen05/TMA/TMEM GEMM family, forced on, against the float64 oracle.
+
+Two comparisons per case: against the oracle on the SAME bf16-rounded operands (isolates the
+kernel: only fp32 accumulation order differs, bound 1e-4 normalised for K up to 8192, plus one
+bf16 rounding of the output where the output is bf16) and against the oracle on the original
+float64 operands (the end-to-end bf16 bound)."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from gpu_util import BF16_ACT_TOL, BF16_GRAD_TOL, rel_err, to_dev, to_np
+
+pytestmark = pytest.mark.gpu
+
+ACC_TOL = 1e-4        # fp32 accumulation vs float64 on identical operands
+BF16_OUT_TOL = 6e-3   # + one round-to-bf16 of the result (2^-8 relative, normalised)
+
+# (B, K, N): one tile, many tiles, ragged M/N/K tails, narrow, K not a multiple of 64
+SHAPES = [(128, 64, 64), (128, 256, 256), (256, 512, 128), (300, 200, 72), (1024, 784, 256), (96, 1024, 520),
+          (2048, 2048, 2048)]
+
+
+@pytest.fixture(autouse=True)
+def _force_tcgen05():
+    from ddnn_b200 import _lib
+    _lib.set_engine(_lib.ENGINE_TCGEN05)
+    yield
+    _lib.set_engine(_lib.ENGINE_AUTO)
+
+
+def _ops(seed, b, k, n):
+    rng = np.random.default_rng(seed)
+    x = rng.random((b, k)) - 0.25
+    w = rng.standard_normal((k, n)) / np.sqrt(k)
+    bias = rng.standard_normal(n) * 0.1
+    dz = rng.standard_normal((b, n)) / b
+    return x, w, bias, dz
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("act", ["relu", "sigmoid", "linear"])
+def test_forward(cuda_device, shape, act):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    x, w, bias, _ = _ops(10, b, k, n)
+    xb, wb = to_dev(x, torch.bfloat16), to_dev(w, torch.bfloat16)
+    ref_same = oracle.activate(np.dot(to_np(xb), to_np(wb)) + bias, act)
+    got32 = ops.dense_forward(xb, wb, to_dev(bias), act, out_dtype=torch.float32)
+    assert rel_err(to_np(got32), ref_same) < ACC_TOL
+    got16 = ops.dense_forward(xb, wb, to_dev(bias), act)
+    assert got16.dtype == torch.bfloat16
+    assert rel_err(to_np(got16), ref_same) < BF16_OUT_TOL
+    assert rel_err(to_np(got16), oracle.activate(np.dot(x, w) + bias, act)) < BF16_ACT_TOL
+
+
+def test_forward_softmax_output(cuda_device):
+    from ddnn_b200 import ops
+    x, w, bias, _ = _ops(11, 64, 256, 512)
+    xb, wb = to_dev(x, torch.bfloat16), to_dev(w, torch.bfloat16)
+    got = ops.dense_forward(xb, wb, to_dev(bias), "softmax")
+    ref = oracle.activate(np.dot(to_np(xb), to_np(wb)) + bias, "softmax")
+    assert got.dtype == torch.float32 and rel_err(to_np(got), ref) < ACC_TOL
+
+
+@pytest.mark.parametrize("shape", SHAPES)
+@pytest.mark.parametrize("act_prev", ["relu", "sigmoid", "linear"])
+def test_backward_dx(cuda_device, shape, act_prev):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    x, w, _, dz = _ops(12, b, k, n)
+    rng = np.random.default_rng(13)
+    zprev = rng.standard_normal((b, k))
+    ab = to_dev(oracle.activate(zprev, act_prev), torch.bfloat16)
+    dzb, wb = to_dev(dz, torch.bfloat16), to_dev(w, torch.bfloat16)
+    a_r = to_np(ab)
+    deriv = {"relu": (a_r > 0).astype(np.float64), "sigmoid": a_r * (1 - a_r), "linear": np.ones_like(a_r)}[act_prev]
+    ref_same = np.dot(to_np(dzb), to_np(wb).T) * deriv
+    got = ops.dense_backward_dx(dzb, wb, ab, act_prev)
+    assert rel_err(to_np(got), ref_same) < BF16_OUT_TOL
+
+
+@pytest.mark.parametrize("shape", SHAPES + [(4096, 784, 256), (8192, 128, 64)])
+def test_backward_dw_and_sgd(cuda_device, shape):
+    from ddnn_b200 import ops
+    b, k, n = shape
+    x, w, bias, dz = _ops(14, b, k, n)
+    xb, dzb = to_dev(x, torch.bfloat16), to_dev(dz, torch.bfloat16)
+    ref_dw = np.dot(to_np(xb).T, to_np(dzb))
+    ref_db = to_np(dzb).sum(axis=0)
+    dw, db = ops.dense_backward_dw(xb, dzb)
+    assert rel_err(to_np(dw), ref_dw) < ACC_TOL
+    assert rel_err(to_np(db), ref_db) < ACC_TOL
+    assert rel_err(to_np(dw), np.dot(x.T, dz)) < BF16_GRAD_TOL
+    # fused SGD epilogue: fp32 master updated in place, bf16 shadow refreshed from it
+    wm, bm = to_dev(w), to_dev(bias)
+    sh = torch.zeros((k, n), dtype=torch.bfloat16, device="cuda")
+    ops.dense_backward_dw_sgd(xb, dzb, wm, bm, 0.5, w_shadow=sh)
+    assert rel_err(to_np(wm), to_np(to_dev(w)) - 0.5 * ref_dw) < 1e-5
+    assert rel_err(to_np(bm), to_np(to_dev(bias)) - 0.5 * ref_db) < 1e-5
+    assert torch.equal(sh, wm.to(torch.bfloat16))
+
+
+def test_dw_deterministic_and_linear(cuda_device):
+    """Size-independent properties at a size the oracle would not finish quickly:
+    run-to-run bit equality, and dW(x, 2*dz) == 2*dW(x, dz) exactly (power-of-two scaling)."""
+    from ddnn_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(0)
+    x = torch.rand((16384, 1024), device="cuda", generator=g).to(torch.bfloat16)
+    dz = torch.randn((16384, 512), device="cuda", generator=g).to(torch.bfloat16)
+    a, da = ops.dense_backward_dw(x, dz)
+    b, _ = ops.dense_backward_dw(x, dz)
+    assert torch.equal(a, b)
+    c, dc = ops.dense_backward_dw(x, dz * 2)
+    assert torch.equal(c, a * 2) and torch.equal(dc, da * 2)
+
+
+def test_forward_full_size_checksum(cuda_device):
+    """8192-wide layer (config 3 shape): rows of X that are one-hot pick rows of W exactly."""
+    from ddnn_b200 import ops
+    n = 8192
+    g = torch.Generator(device="cuda").manual_seed(1)
+    w = (torch.randn((n, n), device="cuda", generator=g) / 90).to(torch.bfloat16)
+    idx = torch.randint(0, n, (512,), device="cuda", generator=g)
+    x = torch.zeros((512, n), device="cuda", dtype=torch.bfloat16)
+    x[torch.arange(512, device="cuda"), idx] = 1
+    out = ops.dense_forward(x, w, torch.zeros(n, device="cuda"), "linear")
+    assert torch.equal(out, w[idx])
+    # and a dense probe against a float64 dot on a few columns
+    xd = torch.rand((256, n), device="cuda", generator=g).to(torch.bfloat16)
+    out = ops.dense_forward(xd, w, torch.zeros(n, device="cuda"), "linear", out_dtype=torch.float32)
+    cols = [0, 1, 255, 256, 4097, 8191]
+    ref = xd.double().cpu().numpy() @ w[:, cols].double().cpu().numpy()
+    assert rel_err(out[:, cols].double().cpu().numpy(), ref) < ACC_TOL
