@@ -17,6 +17,7 @@ OK, ERR_DIM, ERR_ACTIVATION, ERR_CUDA, ERR_ARG, ERR_WORKSPACE, ERR_UNSUPPORTED =
 ACT_LINEAR, ACT_RELU, ACT_SIGMOID, ACT_SOFTMAX = range(4)
 F32, BF16 = 0, 1
 ENGINE_AUTO, ENGINE_SIMT, ENGINE_TCGEN05 = 0, 1, 2
+STATIC_SCRATCH_BYTES = 8 * 1024 * 1024  # DDNN_STATIC_SCRATCH_BYTES
 
 _vp, _i64, _i32, _f32, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_size_t
 
@@ -33,6 +34,8 @@ SYMBOLS = {
     "ddnn_dense_backward_dw_sgd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
                                              _i32, _vp, _sz, _vp]),
     "ddnn_dw_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
+    "ddnn_dense_backward_dw_sgd_static": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
+                                                    _i32, _vp]),
     "ddnn_cast_f32_to_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_cast_bf16_to_f32": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_launch_count": (_i64, []),

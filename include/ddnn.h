@@ -118,6 +118,30 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ,
 
 size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype);
 
+/*
+ * Same computation and arguments as ddnn_dense_backward_dw_sgd, minus the workspace: the
+ * split-K scratch is an array built into the library (DDNN_STATIC_SCRATCH_BYTES per GPU, held
+ * from module load to process exit).  This entry point has no counterpart in the reference.
+ * It exists for hosts that cannot give the library device memory of their own: a process
+ * whose framework has already claimed the GPU's memory for its private pool (a plain
+ * cudaMalloc then fails), an FFI stub that can only forward pointers it was handed, or a
+ * request path on which cudaMalloc/cudaFree are banned because they stall the whole device.
+ *  - Nothing is allocated or freed, here or in anything it calls.
+ *  - Layers whose split-K plan needs more than DDNN_STATIC_SCRATCH_BYTES
+ *    (ddnn_dw_workspace_bytes tells) are refused with DDNN_ERR_WORKSPACE; nothing is launched.
+ *  - The first call on each device looks up the array's device address (one-time set-up, done
+ *    with that device current).  Make that first call before starting any stream capture.
+ *  - All calls share the one array and it keeps the last call's contents; no part of it needs
+ *    to be zero on entry.  Calls that may execute concurrently on the same GPU (different
+ *    streams) race on it: keep them on one stream or order them with events.
+ */
+#define DDNN_STATIC_SCRATCH_BYTES (8u * 1024u * 1024u)
+int ddnn_dense_backward_dw_sgd_static(const void* X, const void* dZ,
+                                      float* W_master, void* W_shadow, float* bias,
+                                      float* dW_out, float* db_out,
+                                      float lr, int apply,
+                                      int64_t B, int64_t K, int64_t N, int dtype, void* stream);
+
 /* out[i] = bf16(in[i]) / fp32(in[i]) converters for staging host-provided fp32 data. */
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
