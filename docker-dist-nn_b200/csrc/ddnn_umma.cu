@@ -24,13 +24,13 @@ constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B row
 constexpr int UMMA_K = 16;
 constexpr int NUM_THREADS = 256;
-constexpr int GROUP_M = 8;  // m-blocks per rasterisation group (L2 reuse of the B operand)
 
 enum { EPI_FWD_BF16 = 0, EPI_FWD_F32 = 1, EPI_DX = 2, EPI_SGD = 3, EPI_STORE = 4 };
 
 struct UmmaParams {
   int M, N;  // output tile space (rows, cols)
   int m_blocks, n_blocks, num_kb, splits, kb_per_split;
+  int group_m;  // m-blocks per rasterisation group: a wave of 148 tiles covers ~group_m x 148/group_m blocks
   const float* bias;
   int act;
   void* out;
@@ -168,10 +168,10 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, const UmmaParams& p) 
   const int per_split = p.m_blocks * p.n_blocks;
   t.ks = tile / per_split;
   const int rem = tile - t.ks * per_split;
-  const int group_sz = GROUP_M * p.n_blocks;
+  const int group_sz = p.group_m * p.n_blocks;
   const int gid = rem / group_sz;
-  const int first_m = gid * GROUP_M;
-  const int gm = min(p.m_blocks - first_m, GROUP_M);
+  const int first_m = gid * p.group_m;
+  const int gm = min(p.m_blocks - first_m, p.group_m);
   const int in_g = rem - gid * group_sz;
   t.m_blk = first_m + in_g % gm;
   t.n_blk = in_g / gm;
@@ -467,6 +467,10 @@ void fill_tiles(UmmaParams& p, int64_t M, int64_t N, int64_t Kred, int bn, int s
   if (splits < 1) splits = 1;
   p.kb_per_split = cdiv(p.num_kb, splits);
   p.splits = cdiv(p.num_kb, p.kb_per_split);  // every split owns >= 1 k-block
+  // Per k-step a wave of 148 concurrent tiles reads (group_m A-blocks of 16 KB) + (148/group_m B-blocks of
+  // bn*128 B) from L2/HBM; the sum is smallest at group_m = sqrt(148 * bn / 128).
+  p.group_m = bn == 256 ? 16 : (bn == 128 ? 12 : 8);
+  if (p.group_m > p.m_blocks) p.group_m = p.m_blocks;
 }
 
 }  // namespace

@@ -100,6 +100,7 @@ class Layer:
         self._rows = 0
         self._bufs = None
         self._ws = None
+        self._gen = 0  # bumped whenever the batch buffers are reallocated (captured graphs go stale)
 
     def _to_dev(self, t) -> torch.Tensor:
         """numpy / list / torch (any device) -> contiguous fp32 tensor on this node's GPU."""
@@ -187,6 +188,7 @@ class Layer:
         }
         self._ws = torch.empty((max(ws_bytes, 256),), dtype=torch.uint8, device=dev)
         self._rows = rows
+        self._gen += 1
 
     def input_buffer(self, row0: int, rows: int) -> torch.Tensor:
         """Rows [row0, row0+rows) of this node's input activation buffer (receive target)."""

@@ -37,6 +37,7 @@ class Trainer:
         self.num_classes = int(self.layer.layer_params[-1]["weights"].shape[1])
         self._graph = None
         self._static = None
+        self._static_gen = -1
         self._pinned = None
 
     # ------------------------------------------------------------------ device-resident step
@@ -68,9 +69,11 @@ class Trainer:
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             loss = self.train_step(sx, sy, lr)
-        self._graph, self._static = g, (sx, sy, loss)
+        self._graph, self._static, self._static_gen = g, (sx, sy, loss), self.layer._gen
 
     def replay(self) -> torch.Tensor:
+        if self._static_gen != self.layer._gen:
+            raise RuntimeError("the batch buffers were reallocated after capture(); capture again")
         self._graph.replay()
         return self._static[2]
 
@@ -78,13 +81,14 @@ class Trainer:
     def static_inputs(self) -> Tuple[torch.Tensor, torch.Tensor]:
         return self._static[0], self._static[1]
 
-    # ------------------------------------------------------------------ end-to-end host call
+    # ------------------------------------------------------------------ end-to-end host calls
     def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor, lr: Optional[float] = None) -> float:
-        """x_host (B, in) fp32 and y_host (B,) int32 in (pinned) HOST memory.  Copies the batch
-        to the device, runs the step (graph replay when captured for this size) and returns
-        the loss as a Python float (a device->host read, so this call synchronises)."""
+        """One synchronous step from HOST data: x_host (B, in) fp32 and y_host (B,) int32 in
+        (pinned) host memory -> H2D copy -> step (graph replay when captured for this size) ->
+        loss read back.  Returns the loss as a Python float, so this call synchronises."""
         rows = x_host.shape[0]
-        if self._graph is not None and self._static[0].shape[0] == rows and lr is None:
+        if (self._graph is not None and self._static[0].shape[0] == rows and lr is None
+                and self._static_gen == self.layer._gen):
             sx, sy, loss = self._static
             sx.copy_(x_host, non_blocking=True)
             sy.copy_(y_host, non_blocking=True)
@@ -95,10 +99,77 @@ class Trainer:
             loss = self.train_step(x, y, lr)
         return float(loss.item())
 
+    def _stream_setup(self, rows: int, lr: Optional[float]) -> None:
+        """Two device staging slots, one captured step per slot, a copy stream and the events
+        that order (H2D of slot s) -> (step on slot s) -> (next H2D into slot s)."""
+        dev = self.device
+        self.layer.begin_batch(rows)
+        key = (rows, lr, self.layer._gen)  # a reallocation of the batch buffers invalidates the graphs
+        if self._pinned is not None and self._pinned["key"] == key:
+            return
+        sx = [torch.zeros((rows, self.in_dim), dtype=torch.float32, device=dev) for _ in range(2)]
+        sy = [torch.zeros((rows,), dtype=torch.int32, device=dev) for _ in range(2)]
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):  # warm-up outside capture (kernel attributes, TMA descriptors), lr = 0
+            self.train_step(sx[0], sy[0], 0.0)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        graphs, loss = [], None
+        for s_ in range(2):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                loss = self.train_step(sx[s_], sy[s_], lr)
+            graphs.append(g)
+        self._pinned = {"key": key, "sx": sx, "sy": sy, "graphs": graphs, "loss": loss,
+                        "copy": torch.cuda.Stream(device=dev),
+                        "h2d": [torch.cuda.Event() for _ in range(2)],
+                        "done": [torch.cuda.Event() for _ in range(2)]}
+
+    def fit_stream(self, batches, lr: Optional[float] = None) -> List[float]:
+        """Trains on a sequence of HOST batches ``(x_pinned fp32 (B, in), y_pinned int32 (B,))``
+        in order.  The H2D copy of batch i+1 runs on a copy stream while batch i computes
+        (double-buffered staging slots, one captured CUDA graph per slot); each step's loss is
+        copied back to pinned host memory asynchronously and all losses are returned after one
+        final synchronisation.  Batches whose row count differs from the first (a ragged tail)
+        run through ``train_step_host``."""
+        batches = list(batches)
+        if not batches:
+            return []
+        dev = self.device
+        rows = batches[0][0].shape[0]
+        self._stream_setup(rows, lr)
+        st = self._pinned
+        losses_host = torch.empty((len(batches),), dtype=torch.float32).pin_memory()
+        tail = {}
+        cur = torch.cuda.current_stream(dev)
+        for ev in st["done"]:
+            ev.record(cur)
+        for i, (hx, hy) in enumerate(batches):
+            if hx.shape[0] != rows:
+                tail[i] = self.train_step_host(hx, hy, lr)
+                continue
+            s_ = i & 1
+            with torch.cuda.stream(st["copy"]):
+                st["copy"].wait_event(st["done"][s_])       # slot free: its previous step has finished
+                st["sx"][s_].copy_(hx, non_blocking=True)
+                st["sy"][s_].copy_(hy, non_blocking=True)
+                st["h2d"][s_].record(st["copy"])
+            cur.wait_event(st["h2d"][s_])
+            st["graphs"][s_].replay()
+            losses_host[i:i + 1].copy_(st["loss"], non_blocking=True)
+            st["done"][s_].record(cur)
+        torch.cuda.synchronize(dev)
+        out = losses_host.tolist()
+        for i, v in tail.items():
+            out[i] = v
+        return out
+
     def fit(self, examples, epochs: Optional[int] = None, batch_size: Optional[int] = None,
             lr: Optional[float] = None) -> List[float]:
-        """Trains on ``{"examples": [{"input", "label"}]}`` data in the reference's batch order
-        (sequential, unshuffled, ragged last batch kept: run_grpc_inference.py:198-205)."""
+        """Trains on ``{"examples": [{"input", "label"}]}`` data (or an ``(x, y)`` pair of
+        arrays) in the reference's batch order: sequential, unshuffled, ragged last batch kept
+        (run_grpc_inference.py:198-205).  Returns the per-step losses."""
         if isinstance(examples, tuple):
             x, y = examples
         else:
@@ -107,10 +178,10 @@ class Trainer:
         batch_size = self.cfg.get("batch_size") if batch_size is None else batch_size
         xs = torch.as_tensor(np.asarray(x), dtype=torch.float32).pin_memory()
         ys = torch.as_tensor(np.asarray(y), dtype=torch.int32).pin_memory()
-        losses = []
+        slices = batch_slices(xs.shape[0], batch_size)
+        losses: List[float] = []
         for _ in range(epochs):
-            for (a, b) in batch_slices(xs.shape[0], batch_size):
-                losses.append(self.train_step_host(xs[a:b], ys[a:b], lr))
+            losses += self.fit_stream([(xs[a:b], ys[a:b]) for (a, b) in slices], lr)
         return losses
 
     # ------------------------------------------------------------------ inference / export
