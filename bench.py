@@ -222,7 +222,7 @@ def timed(fn, steps, warmup, device, barrier=None):
     return e0.elapsed_time(e1)
 
 
-def bench_single(workload, dtype, steps, warmup, device, barrier=None, want_detail=True):
+def bench_single(workload, dtype, steps, warmup, device, barrier=None):
     """All layers on one GPU.  Returns a dict with value/e2e/roofline pieces."""
     import torch
     from ddnn_b200 import Trainer, _lib, ops
@@ -263,9 +263,6 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None, want_deta
     ms = timed(step, steps, warmup, device, barrier)
     res = {"rows": rows, "dims": dims, "dtype": dtype, "ms_total": ms, "launches_per_step": launches_per_step,
            "pool_batches": pool_n, "pool_bytes": pool_n * batch_bytes, "cuda_graph": use_graph}
-    if not want_detail:
-        return res, tr
-
     # ---- e2e: HOST buffers, H2D of the batch + D2H of the loss inside the timed region, through
     # the public call Trainer.train_step_host ----
     hx = [torch.rand((rows, dims[0]), dtype=torch.float32).pin_memory() for _ in range(4)]
@@ -288,7 +285,15 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None, want_deta
     res.update({"e2e_ms_total": ms_e2e, "e2e_steps": e2e_steps, "h2d": rows * dims[0] * 4 + rows * 4, "d2h": 4,
                 "e2e_api": api})
 
-    # ---- dominant-kernel roofline: time every GEMM entry point of the step alone, rotating inputs ----
+    return res, tr
+
+
+def kernel_roofline(tr, rows, dtype, steps, device):
+    """Rank-0 only, no barriers: every GEMM entry point of the step timed alone with CUDA events
+    (L2 flushed before each call, flush time subtracted).  Returns one row per entry point."""
+    import torch
+    from ddnn_b200 import ops
+    elt = 4 if dtype == "f32" else 2
     L = tr.layer
     b = L._bufs
     kern = []
@@ -323,8 +328,7 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None, want_deta
         t_flush = timed(lambda j: flush.zero_(), reps, 3, device)
         t = max(1e-6, (t_both - t_flush) / reps)  # ms per call
         rows_out.append({"kernel": name, "ms": t, "tflops": fl / t / 1e9, "gbs": by / t / 1e6, "flops": fl, "bytes": by})
-    res["kernels"] = rows_out
-    return res, tr
+    return rows_out
 
 
 def bench_pipeline(workload, steps, warmup, device, rank, world, barrier):
@@ -389,8 +393,11 @@ def main():
     device = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=device)
-    barrier = (lambda: dist.barrier()) if world > 1 else None
+        # lazy communicator init (no device_id): each send/recv pair gets its own communicator and
+        # stream, so stage-boundary transfers do not serialise behind each other
+        import datetime
+        dist.init_process_group("nccl", timeout=datetime.timedelta(seconds=240))
+    barrier = (lambda: dist.barrier(device_ids=[local])) if world > 1 else None
 
     def max_over_ranks(ms):
         if world == 1:
@@ -412,12 +419,17 @@ def main():
                "launches_per_step": pr["launches_per_step"], "cuda_graph": False}
         replicas = 1
     else:
-        res, _tr = bench_single(workload, args.dtype, steps, warmup, device, barrier, want_detail=(rank == 0))
+        res, _tr = bench_single(workload, args.dtype, steps, warmup, device, barrier)
+        res["e2e_ms_total"] = max_over_ranks(res["e2e_ms_total"])
+        if rank == 0:
+            res["kernels"] = kernel_roofline(_tr, res["rows"], res["dtype"], steps, device)
         del _tr
         replicas = world
     ms_total = max_over_ranks(res["ms_total"])
     clocks = sampler.stop()
     torch.cuda.empty_cache()
+    if world > 1:
+        dist.barrier(device_ids=[local])
 
     dims, rows = res["dims"], res["rows"]
     value = replicas * rows * steps / (ms_total / 1e3)
@@ -487,8 +499,6 @@ def main():
                 pipes.append({"workload": wl, "error": repr(e)[:300]})
             torch.cuda.empty_cache()
         line["pipeline"] = pipes
-    if world > 1:
-        dist.barrier()
     if rank == 0 and not args.no_extra and world == 1:
         v, desc, ms, n = cpu_train_samples_per_s(workload, args.cpu_budget, warmup=1,
                                                  rows_cap={"narrow65536": 8192, "wide4x8192": 64,
@@ -497,7 +507,7 @@ def main():
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.barrier()
+        dist.barrier(device_ids=[local])
         dist.destroy_process_group()
 
 
