@@ -284,50 +284,96 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None):
         api = "Trainer.train_step_host (pinned host batch -> H2D -> step -> loss D2H)"
     res.update({"e2e_ms_total": ms_e2e, "e2e_steps": e2e_steps, "h2d": rows * dims[0] * 4 + rows * 4, "d2h": 4,
                 "e2e_api": api})
+    return res, tr, xs, ys
 
-    return res, tr
 
-
-def kernel_roofline(tr, rows, dtype, steps, device):
-    """Rank-0 only, no barriers: every GEMM entry point of the step timed alone with CUDA events
-    (L2 flushed before each call, flush time subtracted).  Returns one row per entry point."""
-    import torch
-    from ddnn_b200 import ops
+def _kernel_work(L, rows, dtype):
+    """Algorithmic (FLOPs, bytes) per launch of every entry point of one train step."""
     elt = 4 if dtype == "f32" else 2
-    L = tr.layer
-    b = L._bufs
-    kern = []
-    reps = max(5, min(steps, 50))
+    work = {}
+    n_layers = len(L.layer_params)
     for i, p in enumerate(L.layer_params):
         k, n = p["weights"].shape
-        last = i == len(L.layer_params) - 1
-        act = "linear" if last else p["activation"]
+        last = i == n_layers - 1
+        fl = 2.0 * rows * k * n
+        work[f"forward L{i + 1} {k}->{n}"] = (fl, rows * k * elt + k * n * elt + rows * n * (4 if last else elt))
+        work[f"dX L{i + 1} {n}->{k}"] = (fl, rows * n * elt + k * n * elt + 2 * rows * k * elt)
+        work[f"dW+SGD L{i + 1} {k}x{n}"] = (fl, rows * k * elt + rows * n * elt + 2 * k * n * 4 +
+                                            (k * n * 2 if dtype == "bf16" else 0))
+    n_out = L.layer_params[-1]["weights"].shape[1]
+    work[f"softmax-CE N={n_out}"] = (5.0 * rows * n_out, rows * n_out * (4 + elt) + rows * 8)
+    return work
 
-        def fwd(_j, i=i, p=p, act=act):
-            ops.dense_forward(b["a"][i][:rows], L._w(i), p["biases"], act, out=b["a"][i + 1][:rows])
-        kern.append((f"forward L{i + 1} {k}->{n}", fwd, 2.0 * rows * k * n,
-                     rows * k * elt + k * n * elt + rows * n * (4 if last else elt)))
-        if i > 0:
-            def dx(_j, i=i):
-                ops.dense_backward_dx(b["dz"][i][:rows], L._w(i), b["a"][i][:rows], L.layer_params[i - 1]["activation"],
-                                      out=b["dz"][i - 1][:rows])
-            kern.append((f"dX L{i + 1} {n}->{k}", dx, 2.0 * rows * k * n, rows * n * elt + k * n * elt + 2 * rows * k * elt))
 
-        def dw(_j, i=i, p=p):
-            ops.dense_backward_dw_sgd(b["a"][i][:rows], b["dz"][i][:rows], p["weights"], p["biases"], 0.0,
-                                      w_shadow=L._shadow[i], workspace=L._ws)
-        kern.append((f"dW+SGD L{i + 1} {k}x{n}", dw, 2.0 * rows * k * n,
-                     rows * k * elt + rows * n * elt + 2 * k * n * 4 + (k * n * 2 if dtype == "bf16" else 0)))
-    flush = torch.empty(2 * L2_BYTES, dtype=torch.uint8, device=device)
+def kernel_roofline(tr, xs, ys, dtype, steps, device, use_graph):
+    """Rank-0 only, no barriers: per-entry-point timing with CUDA events on the launch stream.
+
+    Wide nets (kernels of hundreds of microseconds): in situ -- eager train steps on the rotating
+    resident batches with an event pair around every entry-point call.
+    Graph-captured narrow nets (kernels of a few microseconds, where an eager launch is slower than
+    the kernel): every entry point is captured alone into a CUDA graph per resident batch and the
+    graphs are replayed back to back, rotating the batches; intermediates stay where the real step
+    leaves them (L2), the input batch comes from HBM.
+    Returns one row per entry point with its algorithmic FLOPs and bytes per launch."""
+    import torch
+    from ddnn_b200 import ops
+    L = tr.layer
+    rows = xs[0].shape[0]
+    work = _kernel_work(L, rows, dtype)
+    reps = max(5, min(steps, 50))
+    for i in range(3):
+        tr.train_step(xs[i % len(xs)], ys[i % len(xs)])
+    torch.cuda.synchronize(device)
+    acc = {}
+    if not use_graph:
+        L._probe = []
+        for i in range(reps):
+            tr.train_step(xs[i % len(xs)], ys[i % len(xs)])
+        torch.cuda.synchronize(device)
+        spans, L._probe = L._probe, None
+        for name, e0, e1 in spans:
+            acc.setdefault(name, []).append(e0.elapsed_time(e1))
+        how = "CUDA events around the entry point inside eager train steps (in situ)"
+    else:
+        b = L._bufs
+        calls = []
+        n_layers = len(L.layer_params)
+        xin = xs if xs[0].dtype == L.wire_dtype else None  # layer-1 operands straight from the batch pool
+        for i, p in enumerate(L.layer_params):
+            k, n = p["weights"].shape
+            act = "linear" if i == n_layers - 1 else p["activation"]
+            src = (lambda j, i=i: xin[j % len(xin)]) if (i == 0 and xin) else (lambda j, i=i: b["a"][i][:rows])
+            calls.append((f"forward L{i + 1} {k}->{n}", i == 0 and bool(xin),
+                          lambda j, i=i, p=p, act=act, src=src: ops.dense_forward(
+                              src(j), L._w(i), p["biases"], act, out=b["a"][i + 1][:rows])))
+            if i > 0:
+                calls.append((f"dX L{i + 1} {n}->{k}", False,
+                              lambda j, i=i: ops.dense_backward_dx(
+                                  b["dz"][i][:rows], L._w(i), b["a"][i][:rows],
+                                  L.layer_params[i - 1]["activation"], out=b["dz"][i - 1][:rows])))
+            calls.append((f"dW+SGD L{i + 1} {k}x{n}", i == 0 and bool(xin),
+                          lambda j, i=i, p=p, src=src: ops.dense_backward_dw_sgd(
+                              src(j), b["dz"][i][:rows], p["weights"], p["biases"], 0.0, w_shadow=L._shadow[i],
+                              workspace=L._ws)))
+        calls.append((f"softmax-CE N={L.layer_params[-1]['weights'].shape[1]}", False,
+                      lambda j: ops.softmax_ce(b["a"][-1][:rows], ys[j % len(ys)], b["dz"][-1][:rows],
+                                               b["row_loss"][:rows], b["loss"], 1.0 / rows)))
+        for name, rotates, fn in calls:
+            graphs = []
+            for j in range(len(xs) if rotates else 1):
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g):
+                    fn(j)
+                graphs.append(g)
+            ms = timed(lambda j: graphs[j % len(graphs)].replay(), reps * 4, 5, device)
+            acc[name] = [ms / (reps * 4)]
+        how = "each entry point captured alone in a CUDA graph per resident batch, replayed back to back"
     rows_out = []
-    for name, fn, fl, by in kern:
-        def once(j, fn=fn):
-            flush.zero_()  # evict the previous call's operands from L2 (inputs here are not rotated)
-            fn(j)
-        t_both = timed(once, reps, 3, device)
-        t_flush = timed(lambda j: flush.zero_(), reps, 3, device)
-        t = max(1e-6, (t_both - t_flush) / reps)  # ms per call
-        rows_out.append({"kernel": name, "ms": t, "tflops": fl / t / 1e9, "gbs": by / t / 1e6, "flops": fl, "bytes": by})
+    for name, ts in acc.items():
+        t = max(1e-6, float(np.mean(ts)))
+        fl, by = work.get(name, (0.0, 0.0))
+        rows_out.append({"kernel": name, "ms": t, "tflops": fl / t / 1e9, "gbs": by / t / 1e6, "flops": fl,
+                         "bytes": by, "how": how})
     return rows_out
 
 
@@ -419,11 +465,11 @@ def main():
                "launches_per_step": pr["launches_per_step"], "cuda_graph": False}
         replicas = 1
     else:
-        res, _tr = bench_single(workload, args.dtype, steps, warmup, device, barrier)
+        res, _tr, _xs, _ys = bench_single(workload, args.dtype, steps, warmup, device, barrier)
         res["e2e_ms_total"] = max_over_ranks(res["e2e_ms_total"])
         if rank == 0:
-            res["kernels"] = kernel_roofline(_tr, res["rows"], res["dtype"], steps, device)
-        del _tr
+            res["kernels"] = kernel_roofline(_tr, _xs, _ys, res["dtype"], steps, device, res["cuda_graph"])
+        del _tr, _xs, _ys
         replicas = world
     ms_total = max_over_ranks(res["ms_total"])
     clocks = sampler.stop()
@@ -469,7 +515,8 @@ def main():
                     "frac": dom["gbs"] / peaks["hbm_gbs"]}
         roof.update({"traffic": None, "kernel": dom["kernel"], "ms_per_launch": dom["ms"],
                      "peak_source": peaks["source"], "kernel_tflops": dom["tflops"],
-                     "step_share": dom["ms"] / (ms_total / steps)})
+                     "step_share": dom["ms"] / sum(r["ms"] for r in ks),
+                     "timing": dom["how"]})
         line["roofline"] = roof
         line["kernels"] = [{k: (round(v, 6) if isinstance(v, float) else v) for k, v in r.items()
                             if k in ("kernel", "ms", "tflops", "gbs")} for r in ks]

@@ -42,6 +42,11 @@ static bool use_umma(int dtype, int64_t B, int64_t K, int64_t N, std::initialize
   return K >= 64 && N >= 64;
 }
 
+// Skinny kernels (N <= 16): one coalesced pass over the big operand instead of a 64-wide tile.
+static bool use_skinny(int64_t K, int64_t N) {
+  return g_engine.load() == DDNN_ENGINE_AUTO && skinny_ok(K, N);
+}
+
 }  // namespace ddnn
 
 using namespace ddnn;
@@ -90,7 +95,9 @@ int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A,
   }
   cudaStream_t st = (cudaStream_t)stream;
   const int gemm_act = act == DDNN_ACT_SOFTMAX ? DDNN_ACT_LINEAR : act;
-  if (use_umma(dtype, B, K, N, {X, W, A}))
+  if (use_skinny(K, N))
+    rc = skinny_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
+  else if (use_umma(dtype, B, K, N, {X, W, A}))
     rc = umma_forward((const bf16*)X, (const bf16*)W, bias, A, B, K, N, gemm_act, out_dtype, st);
   else
     rc = simt_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
@@ -163,6 +170,7 @@ int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, voi
     return DDNN_ERR_ARG;
   }
   cudaStream_t st = (cudaStream_t)stream;
+  if (use_skinny(K, N)) return skinny_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
   if (use_umma(dtype, B, K, N, {dZ, W, Aprev, dZprev}))
     return umma_dx((const bf16*)dZ, (const bf16*)W, (const bf16*)Aprev, (bf16*)dZprev, B, K, N, act_prev, st);
   return simt_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
@@ -182,6 +190,10 @@ size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
     umma = (s2 > 1 ? s2 * (size_t)K * np : 0) * sizeof(float) + (size_t)colsum_splits(B, N) * np * sizeof(float);
   }
   size_t need = simt > umma ? simt : umma;
+  if (skinny_ok(K, N)) {
+    const size_t sk = (size_t)skinny_dw_splits(B, K, N) * ((size_t)K + 1) * np * sizeof(float);
+    if (sk > need) need = sk;
+  }
   return (need + 255) & ~(size_t)255;
 }
 
@@ -207,6 +219,14 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
   cudaStream_t st = (cudaStream_t)stream;
   const size_t np = np_of(N);
   float* ws = (float*)workspace;
+  if (use_skinny(K, N)) {
+    const int splits = skinny_dw_splits(B, K, N);
+    float* dw_part = ws;
+    float* db_part = ws + (size_t)splits * K * np;
+    rc = skinny_dw_partials(X, dZ, dw_part, db_part, splits, B, K, N, dtype, st);
+    if (rc) return rc;
+    return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+  }
   if (use_umma(dtype, B, K, N, {X, dZ, W_master, W_shadow, dW_out})) {
     const int splits = umma_dw_splits(B, K, N);
     float* dw_part = splits > 1 ? ws : nullptr;

@@ -14,6 +14,16 @@ int simt_dw_partials(const void* X, const void* dZ, float* dw_part, float* db_pa
                      int64_t B, int64_t K, int64_t N, int dtype, cudaStream_t st);
 int simt_dw_splits(int64_t B, int64_t K, int64_t N);
 
+// ---- skinny output layers, N <= 16 (ddnn_skinny.cu) ------------------------------------
+bool skinny_ok(int64_t K, int64_t N);
+int skinny_forward(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K,
+                   int64_t N, int act, int dtype, int out_dtype, cudaStream_t st);
+int skinny_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev, int64_t B, int64_t K,
+              int64_t N, int act_prev, int dtype, cudaStream_t st);
+int skinny_dw_splits(int64_t B, int64_t K, int64_t N);
+int skinny_dw_partials(const void* X, const void* dZ, float* dw_part, float* db_part, int splits,
+                       int64_t B, int64_t K, int64_t N, int dtype, cudaStream_t st);
+
 // ---- split-K reduction + dW epilogue (ddnn_reduce.cu) --------------------------------
 // Sums partials in z order, then SGD (apply) or fp32 store.
 int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K, int64_t N,

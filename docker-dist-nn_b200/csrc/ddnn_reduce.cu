@@ -5,33 +5,54 @@
 namespace ddnn {
 namespace {
 
-// part: [splits][rows][np] fp32.  Row index `rows_w` .. is the bias row (db partials live in
-// a second array).  One thread = 4 consecutive columns, partials summed in z order.
-template <typename EpiW, typename EpiB>
+// dw_part: [splits][rows][np] fp32, db_part: [splits][np] (the bias row).  A group of G lanes
+// (1, 8 or 32) owns 4 consecutive output columns: lane g sums splits g, g+G, ... (loads batched 4
+// at a time), then the G partial sums are combined by a fixed xor-shuffle tree -- the order depends
+// only on (splits, G), so the result is run-to-run deterministic.
+template <int G, typename EpiW, typename EpiB>
 __global__ void __launch_bounds__(256)
 reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part, int splits, int64_t rows,
                  int np, int N, EpiW ew, EpiB eb, bool vecw, bool vecb, int has_db) {
   const int q = np >> 2;
   const int64_t total = (rows + (has_db ? 1 : 0)) * q;
-  for (int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-       idx += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t row = idx / q;
-    const int col = (int)(idx - row * q) * 4;
-    if (col >= N) continue;
-    const int nv = min(4, N - col);
+  const int sub = threadIdx.x % G;
+  const int64_t groups = (int64_t)gridDim.x * blockDim.x / G;
+  const int64_t g0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  // uniform trip count for every thread: the shuffles below are executed by whole warps
+  for (int64_t it = 0; it * groups < total; ++it) {
+    const int64_t idx = g0 + it * groups;
+    const bool active = idx < total;
+    const int64_t row = active ? idx / q : 0;
+    const int col = active ? (int)(idx - row * q) * 4 : 0;
+    const bool is_w = row < rows;
+    const float* base = is_w ? dw_part + row * np + col : db_part + col;
+    const int64_t zs = is_w ? rows * np : np;
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (row < rows) {
-      for (int z = 0; z < splits; ++z) {
-        float4 v = ld4(dw_part + ((int64_t)z * rows + row) * np + col);
+    if (active) {
+      int z = sub;
+      for (; z + 3 * G < splits; z += 4 * G) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = ld4(base + (int64_t)(z + u * G) * zs);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      }
+      for (; z < splits; z += G) {
+        float4 v = ld4(base + (int64_t)z * zs);
         s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       }
-      ew.apply4(row, col, s, nv, vecw);
-    } else {
-      for (int z = 0; z < splits; ++z) {
-        float4 v = ld4(db_part + (int64_t)z * np + col);
-        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
-      }
-      eb.apply4(0, col, s, nv, vecb);
+    }
+#pragma unroll
+    for (int o = G / 2; o > 0; o >>= 1) {
+      s.x += __shfl_xor_sync(0xffffffffu, s.x, o);
+      s.y += __shfl_xor_sync(0xffffffffu, s.y, o);
+      s.z += __shfl_xor_sync(0xffffffffu, s.z, o);
+      s.w += __shfl_xor_sync(0xffffffffu, s.w, o);
+    }
+    if (active && sub == 0 && col < N) {
+      const int nv = min(4, N - col);
+      if (is_w) ew.apply4(row, col, s, nv, vecw);
+      else eb.apply4(0, col, s, nv, vecb);
     }
   }
 }
@@ -88,21 +109,31 @@ int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K,
   const int has_db = db_part != nullptr;
   const int64_t total = (rows + has_db) * (np / 4);
   if (total == 0) return DDNN_OK;
-  int blocks = (int)((total + 255) / 256);
+  const int G = splits <= 8 ? 1 : (splits <= 64 ? 8 : 32);
+  // grid: whole groups per block; the grid-stride loop needs gridDim*256 to be a multiple of G (it is)
+  long blocks = (long)((total * G + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
+#define DDNN_REDUCE(GG, EW, EB, ew, eb, vw, vb)                                                              \
+  reduce_dw_kernel<GG, EW, EB><<<(unsigned)blocks, 256, 0, st>>>(dw_part, db_part, splits, rows, np, (int)N, ew, \
+                                                              eb, vw, vb, has_db)
   if (apply) {
     EpiSgd ew{W_master, (bf16*)W_shadow, N, lr};
     EpiSgd eb{bias, nullptr, N, lr};
     const bool vw = vec_ok(W_master, N) && (!W_shadow || vec_ok((bf16*)W_shadow, N));
-    reduce_dw_kernel<EpiSgd, EpiSgd><<<blocks, 256, 0, st>>>(dw_part, db_part, splits, rows, np, (int)N, ew, eb, vw,
-                                                           vec_ok(bias, N), has_db);
+    const bool vb = vec_ok(bias, N);
+    if (G == 1) DDNN_REDUCE(1, EpiSgd, EpiSgd, ew, eb, vw, vb);
+    else if (G == 8) DDNN_REDUCE(8, EpiSgd, EpiSgd, ew, eb, vw, vb);
+    else DDNN_REDUCE(32, EpiSgd, EpiSgd, ew, eb, vw, vb);
   } else {
     EpiStoreF32 ew{dW_out, N};
     EpiStoreF32 eb{db_out, N};
-    reduce_dw_kernel<EpiStoreF32, EpiStoreF32><<<blocks, 256, 0, st>>>(dw_part, db_part, splits, rows, np, (int)N, ew, eb,
-                                                                     vec_ok(dW_out, N), vec_ok(db_out, N), has_db);
+    const bool vw = vec_ok(dW_out, N), vb = vec_ok(db_out, N);
+    if (G == 1) DDNN_REDUCE(1, EpiStoreF32, EpiStoreF32, ew, eb, vw, vb);
+    else if (G == 8) DDNN_REDUCE(8, EpiStoreF32, EpiStoreF32, ew, eb, vw, vb);
+    else DDNN_REDUCE(32, EpiStoreF32, EpiStoreF32, ew, eb, vw, vb);
   }
+#undef DDNN_REDUCE
   count_launch();
   DDNN_LAUNCH_CHECK();
   return DDNN_OK;

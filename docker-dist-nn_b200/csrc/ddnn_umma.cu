@@ -157,7 +157,10 @@ struct Cfg {
   static constexpr uint32_t B_BYTES = BN * BLOCK_K * 2;
   static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr uint32_t TMEM_COLS = 2 * BN;
-  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + (2 * STAGES + 4) * 8 + 16;
+  static constexpr uint32_t STG_PITCH = 36;                       // floats per staged row (16-B aligned, conflict-free)
+  static constexpr uint32_t STG_BYTES = 4 * 32 * STG_PITCH * 4;   // one 32x32 fp32 transpose buffer per epilogue warp
+  static constexpr uint32_t BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES;
 };
 
 struct TileCoord {
@@ -286,40 +289,104 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   } else if (warp >= 4) {
     // ===================== epilogue =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
+    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * 32 * C::STG_PITCH;
     uint32_t as = 0, aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const TileCoord t = decode_tile(tile, p);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
-      const int row = t.m_blk * BLOCK_M + q * 32 + lane;
-      const bool row_ok = row < p.M;
-      const int64_t orow = (int64_t)row + (EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0);
+      // Each thread holds one accumulator ROW (TMEM lane) x 32 columns.  A 32x32 transpose through
+      // shared memory regroups that as lane = (row r8 = lane/4, 8 consecutive columns cg = lane%4): one
+      // warp instruction then touches 8 rows x 64 B (bf16) / 128 B (fp32) contiguous per row, every
+      // global access is a 16-byte vector, and a lane issues its 4 row-loads (A_prev / W) together.
+      const int row0 = t.m_blk * BLOCK_M + q * 32;
+      const int nrows = min(32, p.M - row0);  // warp-uniform
+      const int64_t zoff = EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0;
+      const int cg = lane & 3, r8 = lane >> 2;
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         float v[32];
         tmem_ld32(tmem_base + as * BN + c * 32 + ((uint32_t)(q * 32) << 16), v);
         tmem_ld_wait();
-        const int col0 = t.n_blk * BN + c * 32;
-        if (row_ok) {
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const int col = col0 + j * 4;
-            if (col < p.N) {
-              const float4 x = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-              if (EPI == EPI_FWD_BF16) {
-                EpiFwd<bf16>{p.bias, (bf16*)p.out, p.N, p.act}.apply4(orow, col, x, 4, true);
-              } else if (EPI == EPI_FWD_F32) {
-                EpiFwd<float>{p.bias, (float*)p.out, p.N, p.act}.apply4(orow, col, x, 4, true);
-              } else if (EPI == EPI_DX) {
-                EpiDx<bf16>{p.aprev, (bf16*)p.out, p.N, p.act}.apply4(orow, col, x, 4, true);
-              } else if (EPI == EPI_SGD) {
-                EpiSgd{p.w_master, p.w_shadow, p.N, p.lr}.apply4(orow, col, x, 4, true);
-              } else {
-                EpiStoreF32{(float*)p.out, p.N}.apply4(orow, col, x, 4, true);
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(&stg[lane * C::STG_PITCH + 4 * j]) =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+        const int col = t.n_blk * BN + c * 32 + cg * 8;  // N % 8 == 0: a group of 8 columns is all in or all out
+        if (col < p.N) {
+          const int64_t idx0 = ((int64_t)row0 + zoff) * p.N + col;
+          float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+          if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+            b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+            b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+          }
+          uint4 ap[4];         // EPI_DX: 8 bf16 of A_prev per row
+          float4 w0[4], w1[4];  // EPI_SGD: 8 fp32 of W_master per row
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + r8;
+            if (EPI == EPI_DX) {
+              ap[it] = make_uint4(0, 0, 0, 0);
+              if (p.act != DDNN_ACT_LINEAR && r < nrows)
+                ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
+            }
+            if (EPI == EPI_SGD) {
+              w0[it] = w1[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (r < nrows) {
+                w0[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N);
+                w1[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N + 4);
+              }
+            }
+          }
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = it * 8 + r8;
+            if (r >= nrows) continue;
+            const float4 x0 = *reinterpret_cast<const float4*>(&stg[r * C::STG_PITCH + cg * 8]);
+            const float4 x1 = *reinterpret_cast<const float4*>(&stg[r * C::STG_PITCH + cg * 8 + 4]);
+            float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+            const int64_t idx = idx0 + (int64_t)r * p.N;
+            if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+              for (int e = 0; e < 8; ++e) x[e] = act_fwd(x[e] + bb[e], p.act);
+            } else if (EPI == EPI_DX) {
+              if (p.act != DDNN_ACT_LINEAR) {
+                const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&ap[it]);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const float2 a = __bfloat1622float2(a2[e]);
+                  x[2 * e] *= act_bwd(a.x, p.act);
+                  x[2 * e + 1] *= act_bwd(a.y, p.act);
+                }
+              }
+            } else if (EPI == EPI_SGD) {
+              const float ww[8] = {w0[it].x, w0[it].y, w0[it].z, w0[it].w, w1[it].x, w1[it].y, w1[it].z, w1[it].w};
+#pragma unroll
+              for (int e = 0; e < 8; ++e) x[e] = ww[e] - p.lr * x[e];
+            }
+            if (EPI == EPI_FWD_BF16 || EPI == EPI_DX) {
+              uint4 o;
+              __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+              *reinterpret_cast<uint4*>((bf16*)p.out + idx) = o;
+            } else {
+              float* dst = EPI == EPI_SGD ? p.w_master + idx : (float*)p.out + idx;
+              *reinterpret_cast<float4*>(dst) = make_float4(x[0], x[1], x[2], x[3]);
+              *reinterpret_cast<float4*>(dst + 4) = make_float4(x[4], x[5], x[6], x[7]);
+              if (EPI == EPI_SGD && p.w_shadow) {
+                uint4 o;
+                __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+                *reinterpret_cast<uint4*>(p.w_shadow + idx) = o;
               }
             }
           }
         }
+        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();

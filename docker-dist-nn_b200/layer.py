@@ -35,6 +35,33 @@ def _device(device) -> torch.device:
     return torch.device(device)
 
 
+class _NullSpan:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NULL_SPAN = _NullSpan()
+
+
+class _Span:
+    def __init__(self, sink, name, device):
+        self.sink, self.name, self.device = sink, name, device
+
+    def __enter__(self):
+        self.e0 = torch.cuda.Event(enable_timing=True)
+        self.e0.record(torch.cuda.current_stream(self.device))
+        return self
+
+    def __exit__(self, *a):
+        e1 = torch.cuda.Event(enable_timing=True)
+        e1.record(torch.cuda.current_stream(self.device))
+        self.sink.append((self.name, self.e0, e1))
+        return False
+
+
 class Layer:
     def __init__(self, dtype: Optional[str] = None, device=None):
         # grpc_node.py:17-58 -- identical environment contract and failure behaviour
@@ -101,12 +128,18 @@ class Layer:
         self._bufs = None
         self._ws = None
         self._gen = 0  # bumped whenever the batch buffers are reallocated (captured graphs go stale)
+        self._probe = None  # bench.py: list collecting (name, start_event, end_event) per entry-point call
 
     def _to_dev(self, t) -> torch.Tensor:
         """numpy / list / torch (any device) -> contiguous fp32 tensor on this node's GPU."""
         if isinstance(t, torch.Tensor):
             return t.detach().to(device=self.device, dtype=torch.float32).contiguous()
         return torch.as_tensor(np.asarray(t), dtype=torch.float32).contiguous().to(self.device)
+
+    def _span(self, name: str):
+        """CUDA-event bracket around one entry-point call while a probe list is attached
+        (in-situ kernel timing for bench.py); a no-op context otherwise."""
+        return _Span(self._probe, name, self.device) if self._probe is not None else _NULL_SPAN
 
     @property
     def wire_dtype(self) -> torch.dtype:
@@ -187,6 +220,10 @@ class Layer:
             "loss": torch.zeros((1,), dtype=torch.float32, device=dev),
         }
         self._ws = torch.empty((max(ws_bytes, 256),), dtype=torch.uint8, device=dev)
+        # second workspace: the side-stream dW GEMMs of backward_and_step must not share scratch with dW_1
+        ws2 = max([ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp[1:]],
+                  default=0)
+        self._ws_side = torch.empty((max(ws2, 256),), dtype=torch.uint8, device=dev)
         self._rows = rows
         self._gen += 1
 
@@ -226,7 +263,9 @@ class Layer:
                 act = "linear"  # logits; softmax happens inside the fused CE kernel
             elif act == "softmax":
                 raise ValueError("hidden softmax layers are not supported in training (row Jacobian)")
-            ops.dense_forward(a[i][row0:row0 + rows], self._w(i), p["biases"], act, out=a[i + 1][row0:row0 + rows])
+            k_, n_ = p["weights"].shape
+            with self._span(f"forward L{i + 1} {k_}->{n_}"):
+                ops.dense_forward(a[i][row0:row0 + rows], self._w(i), p["biases"], act, out=a[i + 1][row0:row0 + rows])
         return a[-1][row0:row0 + rows]
 
     def loss_and_grad(self, labels: torch.Tensor, row0: int = 0, denom: Optional[int] = None,
@@ -239,8 +278,9 @@ class Layer:
         rows = labels.numel()
         denom = rows if denom is None else denom
         b = self._bufs
-        ops.softmax_ce(b["a"][-1][row0:row0 + rows], labels, b["dz"][-1][row0:row0 + rows],
-                       b["row_loss"][row0:row0 + rows], b["loss"], 1.0 / float(denom), accumulate=accumulate)
+        with self._span(f"softmax-CE N={b['a'][-1].shape[1]}"):
+            ops.softmax_ce(b["a"][-1][row0:row0 + rows], labels, b["dz"][-1][row0:row0 + rows],
+                           b["row_loss"][row0:row0 + rows], b["loss"], 1.0 / float(denom), accumulate=accumulate)
         return b["loss"]
 
     def backward(self, row0: int = 0, rows: Optional[int] = None, need_input_grad: bool = True
@@ -252,11 +292,15 @@ class Layer:
         b = self._bufs
         sl = slice(row0, row0 + rows)
         for i in range(len(self.layer_params) - 1, 0, -1):
-            ops.dense_backward_dx(b["dz"][i][sl], self._w(i), b["a"][i][sl], self.layer_params[i - 1]["activation"],
-                                  out=b["dz"][i - 1][sl])
+            k_, n_ = self.layer_params[i]["weights"].shape
+            with self._span(f"dX L{i + 1} {n_}->{k_}"):
+                ops.dense_backward_dx(b["dz"][i][sl], self._w(i), b["a"][i][sl],
+                                      self.layer_params[i - 1]["activation"], out=b["dz"][i - 1][sl])
         if not need_input_grad:
             return None
-        ops.dense_backward_dx(b["dz"][0][sl], self._w(0), b["a"][0][sl], self.input_activation, out=b["dx"][sl])
+        k_, n_ = self.layer_params[0]["weights"].shape
+        with self._span(f"dX L1 {n_}->{k_}"):
+            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), b["a"][0][sl], self.input_activation, out=b["dx"][sl])
         return b["dx"][sl]
 
     def step(self, lr: float, rows: Optional[int] = None) -> None:
@@ -265,8 +309,42 @@ class Layer:
         rows = self._rows if rows is None else rows
         b = self._bufs
         for i, p in enumerate(self.layer_params):
-            ops.dense_backward_dw_sgd(b["a"][i][:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
-                                      w_shadow=self._shadow[i], workspace=self._ws)
+            k_, n_ = p["weights"].shape
+            with self._span(f"dW+SGD L{i + 1} {k_}x{n_}"):
+                ops.dense_backward_dw_sgd(b["a"][i][:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
+                                          w_shadow=self._shadow[i], workspace=self._ws)
+
+    def backward_and_step(self, lr: float, rows: Optional[int] = None, side: Optional[torch.cuda.Stream] = None) -> None:
+        """backward() + step() for a single-node model with the weight updates of the upper layers
+        running on ``side`` beside the dX chain: dW_l starts as soon as dX_l (the last reader of the
+        old W_l) has finished, so only  dX_L .. dX_2 -> dW_1  stays on the critical path.  Works
+        eagerly and under CUDA-graph capture (the cross-stream events become graph edges)."""
+        rows = self._rows if rows is None else rows
+        if side is None or len(self.layer_params) < 2:
+            self.backward(0, rows, need_input_grad=False)
+            self.step(lr, rows)
+            return
+        b = self._bufs
+        main = torch.cuda.current_stream(self.device)
+        sl = slice(0, rows)
+        for i in range(len(self.layer_params) - 1, 0, -1):
+            p = self.layer_params[i]
+            k_, n_ = p["weights"].shape
+            with self._span(f"dX L{i + 1} {n_}->{k_}"):
+                ops.dense_backward_dx(b["dz"][i][sl], self._w(i), b["a"][i][sl],
+                                      self.layer_params[i - 1]["activation"], out=b["dz"][i - 1][sl])
+            ev = torch.cuda.Event()
+            ev.record(main)
+            side.wait_event(ev)
+            with torch.cuda.stream(side):
+                ops.dense_backward_dw_sgd(b["a"][i][sl], b["dz"][i][sl], p["weights"], p["biases"], lr,
+                                          w_shadow=self._shadow[i], workspace=self._ws_side)
+        p = self.layer_params[0]
+        k_, n_ = p["weights"].shape
+        with self._span(f"dW+SGD L1 {k_}x{n_}"):
+            ops.dense_backward_dw_sgd(b["a"][0][sl], b["dz"][0][sl], p["weights"], p["biases"], lr,
+                                      w_shadow=self._shadow[0], workspace=self._ws)
+        main.wait_stream(side)
 
     def gradients(self, rows: Optional[int] = None):
         """[(dW, db)] per local layer from the buffered activations/gradients (no update)."""

@@ -35,6 +35,7 @@ class Trainer:
         self.device = self.layer.device
         self.in_dim = in_dim
         self.num_classes = int(self.layer.layer_params[-1]["weights"].shape[1])
+        self._side = torch.cuda.Stream(device=self.device)  # upper-layer dW GEMMs run beside the dX chain
         self._graph = None
         self._static = None
         self._static_gen = -1
@@ -48,8 +49,7 @@ class Trainer:
         L.begin_batch(x.shape[0])
         L.forward_train(x, 0)
         loss = L.loss_and_grad(labels, 0)
-        L.backward(0, x.shape[0], need_input_grad=False)
-        L.step(self.lr if lr is None else lr, x.shape[0])
+        L.backward_and_step(self.lr if lr is None else lr, x.shape[0], side=self._side)
         return loss
 
     def capture(self, rows: int, lr: Optional[float] = None, x_dtype: torch.dtype = torch.float32) -> None:

@@ -165,3 +165,48 @@ def test_bf16_simt_engine(cuda_device, shape):
         assert rel_err(to_np(dx), np.dot(dz, w.T)) < BF16_ACT_TOL
     finally:
         _lib.set_engine(_lib.ENGINE_AUTO)
+
+
+@pytest.mark.parametrize("shape", [(50, 64, 10), (257, 100, 130), (33, 20, 5)])
+def test_simt_engine_f32_forced(cuda_device, shape):
+    """The generic register-tiled kernels on shapes that AUTO routes to the skinny kernels."""
+    from ddnn_b200 import _lib, ops
+    b, k, n = shape
+    x, w, bias = _data(b, k, n, seed=8)
+    rng = np.random.default_rng(9)
+    dz = rng.standard_normal((b, n)) / b
+    _lib.set_engine(_lib.ENGINE_SIMT)
+    try:
+        got = ops.dense_forward(to_dev(x), to_dev(w), to_dev(bias), "sigmoid")
+        assert rel_err(to_np(got), oracle.activate(np.dot(x, w) + bias, "sigmoid")) < F32_TOL
+        dw, db = ops.dense_backward_dw(to_dev(x), to_dev(dz))
+        assert rel_err(to_np(dw), np.dot(x.T, dz)) < F32_TOL and rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+        dx = ops.dense_backward_dx(to_dev(dz), to_dev(w), None, "linear")
+        assert rel_err(to_np(dx), np.dot(dz, w.T)) < F32_TOL
+    finally:
+        _lib.set_engine(_lib.ENGINE_AUTO)
+
+
+@pytest.mark.parametrize("bkn", [(65536, 256, 10), (4096, 64, 10), (777, 300, 16), (100, 1000, 1), (64, 5, 13)])
+@pytest.mark.parametrize("dt", ["f32", "bf16"])
+def test_skinny_output_layer_kernels(cuda_device, bkn, dt):
+    """N <= 16 layers (the 10-class softmax layer): forward, dX, dW/db at narrow-config sizes."""
+    from ddnn_b200 import ops
+    b, k, n = bkn
+    tdt = torch.float32 if dt == "f32" else torch.bfloat16
+    rng = np.random.default_rng(10)
+    x = rng.random((b, k)) - 0.25
+    w = rng.standard_normal((k, n)) / np.sqrt(k)
+    bias = rng.standard_normal(n) * 0.1
+    dz = rng.standard_normal((b, n)) / b
+    a_prev = oracle.activate(rng.standard_normal((b, k)), "relu")
+    xd, wd, dzd, ad = (to_dev(t, tdt) for t in (x, w, dz, a_prev))
+    xr, wr, dzr, ar = (to_np(t) for t in (xd, wd, dzd, ad))  # operands as the kernel sees them
+    got = ops.dense_forward(xd, wd, to_dev(bias), "linear", out_dtype=torch.float32)
+    assert rel_err(to_np(got), np.dot(xr, wr) + bias) < F32_TOL
+    dw, db = ops.dense_backward_dw(xd, dzd)
+    assert rel_err(to_np(dw), np.dot(xr.T, dzr)) < F32_TOL
+    assert rel_err(to_np(db), dzr.sum(axis=0)) < F32_TOL
+    dx = ops.dense_backward_dx(dzd, wd, ad, "relu")
+    ref = np.dot(dzr, wr.T) * (ar > 0)
+    assert rel_err(to_np(dx), ref) < (F32_TOL if dt == "f32" else 6e-3)
