@@ -59,6 +59,106 @@ skinny_fwd_kernel(const TI* __restrict__ X, const TI* __restrict__ W, const floa
   }
 }
 
+// Vector variant of the forward (rows 16-byte aligned: K % E == 0, E = elements per 16 bytes):
+// 4 lanes share a row, a warp covers 8 rows per iteration.  Lane g of a row loads the 16-byte
+// chunks g, g+4, g+8, ... (all of them up front: up to 8 loads in flight per lane), multiplies
+// against W rows staged in shared memory in a permuted order (the 4 rows read together by the 4
+// lanes of a group sit next to each other -> conflict-free), and the 4 partial sums per output are
+// combined with 2 shuffle steps.
+template <typename T> struct Chunk;
+template <> struct Chunk<float> { static constexpr int E = 4; };
+template <> struct Chunk<bf16> { static constexpr int E = 8; };
+
+template <typename T>
+__device__ __forceinline__ void unpack16(const uint4& r, float* x) {
+  if (Chunk<T>::E == 4) {
+    x[0] = __uint_as_float(r.x); x[1] = __uint_as_float(r.y); x[2] = __uint_as_float(r.z); x[3] = __uint_as_float(r.w);
+  } else {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __bfloat1622float2(h[e]);
+      x[2 * e] = f.x; x[2 * e + 1] = f.y;
+    }
+  }
+}
+
+template <int NV4, int MAXC, typename TI, typename TO>
+__global__ void __launch_bounds__(256)
+skinny_fwd_vec_kernel(const TI* __restrict__ X, const TI* __restrict__ W, const float* __restrict__ bias,
+                      TO* __restrict__ out, int64_t B, int K, int N, int act) {
+  constexpr int E = Chunk<TI>::E;
+  // [Kp][WPITCH] with Kp = K rounded up to 4E; row k is stored at s(k) = (k / 4E) * 4E + (k % E) * 4 + (k / E) % 4,
+  // rows of the last partial group that no k maps to stay zero
+  extern __shared__ float ws[];
+  const int Kp = (K + 4 * E - 1) / (4 * E) * (4 * E);
+  for (int i = threadIdx.x; i < Kp * WPITCH; i += blockDim.x) ws[i] = 0.f;
+  __syncthreads();
+  for (int i = threadIdx.x; i < K * 16; i += blockDim.x) {
+    const int k = i >> 4, n = i & 15;
+    const int srow = (k / (4 * E)) * (4 * E) + (k % E) * 4 + (k / E) % 4;
+    if (n < N) ws[srow * WPITCH + n] = ld1(W + (int64_t)k * N + n);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+  const int g = lane & 3, rsub = lane >> 2;
+  const int nchunks = K / E;               // 16-byte chunks per row
+  const int per_lane = (nchunks + 3) / 4;  // <= MAXC
+  for (int64_t r0 = ((int64_t)blockIdx.x * wpb + warp) * 8; r0 < B; r0 += (int64_t)gridDim.x * wpb * 8) {
+    const int64_t row = r0 + rsub;
+    const bool row_ok = row < B;
+    uint4 raw[MAXC];
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      raw[i] = make_uint4(0, 0, 0, 0);
+      const int ch = g + 4 * i;
+      if (row_ok && i < per_lane && ch < nchunks) raw[i] = *reinterpret_cast<const uint4*>(X + row * K + ch * E);
+    }
+    float acc[NV4 * 4];
+#pragma unroll
+    for (int j = 0; j < NV4 * 4; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXC; ++i) {
+      if (i < per_lane) {  // warp-uniform
+        float x[E];
+        unpack16<TI>(raw[i], x);
+        // chunk (g + 4i) covers k = (g + 4i) * E + j  ->  s = i * 4E + j * 4 + g  (< Kp; rows past K hold zeros)
+#pragma unroll
+        for (int j = 0; j < E; ++j) {
+          const float4* wr = reinterpret_cast<const float4*>(ws + (i * 4 * E + j * 4 + g) * WPITCH);
+#pragma unroll
+          for (int q = 0; q < NV4; ++q) {
+            const float4 w = wr[q];
+            acc[4 * q + 0] = fmaf(x[j], w.x, acc[4 * q + 0]);
+            acc[4 * q + 1] = fmaf(x[j], w.y, acc[4 * q + 1]);
+            acc[4 * q + 2] = fmaf(x[j], w.z, acc[4 * q + 2]);
+            acc[4 * q + 3] = fmaf(x[j], w.w, acc[4 * q + 3]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NV4 * 4; ++j) {
+      acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+      acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+    }
+    // lane g of the row writes outputs g, g+4, g+8, g+12
+    if (row_ok) {
+#pragma unroll
+      for (int q = 0; q < NV4; ++q) {
+        const int n = g + 4 * q;
+        float v = acc[4 * q];
+#pragma unroll
+        for (int e = 1; e < 4; ++e)
+          if (g == e) v = acc[4 * q + e];
+        // acc[4q + e] holds output column 4q + e; lane g takes e = g  -> column 4q + g
+        if (4 * q + g < N) out[row * N + 4 * q + g] = from_f32<TO>(act_fwd(v + __ldg(bias + 4 * q + g), act));
+        (void)n;
+      }
+    }
+  }
+}
+
 template <int NV4, typename T>
 __global__ void __launch_bounds__(256)
 skinny_dx_kernel(const T* __restrict__ dZ, const T* __restrict__ W, const T* __restrict__ Aprev, T* __restrict__ out,
@@ -79,19 +179,28 @@ skinny_dx_kernel(const T* __restrict__ dZ, const T* __restrict__ W, const T* __r
     }
     __syncthreads();
     if (k < K) {
-      for (int r = 0; r < nr; ++r) {
-        float acc = 0.f;
 #pragma unroll
-        for (int q = 0; q < NV4; ++q) {
-          const float4 d = *reinterpret_cast<const float4*>(&dzs[r][4 * q]);
-          acc = fmaf(d.x, w[4 * q], acc);
-          acc = fmaf(d.y, w[4 * q + 1], acc);
-          acc = fmaf(d.z, w[4 * q + 2], acc);
-          acc = fmaf(d.w, w[4 * q + 3], acc);
+      for (int rg = 0; rg < ROWS_TILE; rg += 8) {
+        float a8[8];  // the 8 A_prev loads of this group are issued before the first use
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          a8[u] = (act != DDNN_ACT_LINEAR && rg + u < nr) ? ld1(Aprev + (rb + rg + u) * K + k) : 1.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (rg + u < nr) {
+            float acc = 0.f;
+#pragma unroll
+            for (int q = 0; q < NV4; ++q) {
+              const float4 d = *reinterpret_cast<const float4*>(&dzs[rg + u][4 * q]);
+              acc = fmaf(d.x, w[4 * q], acc);
+              acc = fmaf(d.y, w[4 * q + 1], acc);
+              acc = fmaf(d.z, w[4 * q + 2], acc);
+              acc = fmaf(d.w, w[4 * q + 3], acc);
+            }
+            const float gq = act == DDNN_ACT_LINEAR ? 1.f : act_bwd(a8[u], act);
+            out[(rb + rg + u) * K + k] = from_f32<T>(acc * gq);
+          }
         }
-        const int64_t o = (rb + r) * K + k;
-        const float g = act == DDNN_ACT_LINEAR ? 1.f : act_bwd(ld1(Aprev + o), act);
-        out[o] = from_f32<T>(acc * g);
       }
     }
   }
@@ -121,16 +230,21 @@ skinny_dw_kernel(const T* __restrict__ X, const T* __restrict__ dZ, float* __res
     if (blockIdx.y == 0 && threadIdx.x < 16)
       for (int r = 0; r < nr; ++r) dbs += dzs[r][threadIdx.x];
     if (k < K) {
-#pragma unroll 4
-      for (int r = 0; r < nr; ++r) {
-        const float x = ld1(X + (rb + r) * K + k);
 #pragma unroll
-        for (int q = 0; q < NV4; ++q) {
-          const float4 d = *reinterpret_cast<const float4*>(&dzs[r][4 * q]);
-          acc[4 * q + 0] = fmaf(x, d.x, acc[4 * q + 0]);
-          acc[4 * q + 1] = fmaf(x, d.y, acc[4 * q + 1]);
-          acc[4 * q + 2] = fmaf(x, d.z, acc[4 * q + 2]);
-          acc[4 * q + 3] = fmaf(x, d.w, acc[4 * q + 3]);
+      for (int rg = 0; rg < ROWS_TILE; rg += 8) {
+        float x8[8];  // 8 independent loads in flight before the FMAs (rows past nr contribute x = 0)
+#pragma unroll
+        for (int u = 0; u < 8; ++u) x8[u] = rg + u < nr ? ld1(X + (rb + rg + u) * K + k) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+#pragma unroll
+          for (int q = 0; q < NV4; ++q) {
+            const float4 d = *reinterpret_cast<const float4*>(&dzs[rg + u][4 * q]);
+            acc[4 * q + 0] = fmaf(x8[u], d.x, acc[4 * q + 0]);
+            acc[4 * q + 1] = fmaf(x8[u], d.y, acc[4 * q + 1]);
+            acc[4 * q + 2] = fmaf(x8[u], d.z, acc[4 * q + 2]);
+            acc[4 * q + 3] = fmaf(x8[u], d.w, acc[4 * q + 3]);
+          }
         }
       }
     }
@@ -148,28 +262,50 @@ int nv4_of(int64_t N) { return (int)((N + 3) / 4); }
 
 }  // namespace
 
-bool skinny_ok(int64_t K, int64_t N) { return N >= 1 && N <= 16 && K >= 1 && K * WPITCH * 4 <= 160 * 1024; }
+bool skinny_ok(int64_t K, int64_t N) { return N >= 1 && N <= 16 && K >= 1 && (K + 32) * WPITCH * 4 <= 160 * 1024; }
 
 template <typename TI, typename TO>
 static int skinny_fwd_t(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K, int64_t N,
                         int act, cudaStream_t st) {
-  const size_t smem = (size_t)K * WPITCH * sizeof(float);
-  long blocks = (B + 7) / 8;
+  constexpr int E = Chunk<TI>::E;
+  const size_t smem = (size_t)((K + 4 * E - 1) / (4 * E) * (4 * E)) * WPITCH * sizeof(float);
+  const bool vec = (K % E == 0) && (K / E <= 4 * 8) && (reinterpret_cast<uintptr_t>(X) % 16 == 0);
+  long blocks = vec ? (B + 63) / 64 : (B + 7) / 8;
   if (blocks > 148 * 4) blocks = 148 * 4;
-#define DDNN_SK_FWD(NV)                                                                                        \
-  do {                                                                                                         \
-    auto kern = skinny_fwd_kernel<NV, TI, TO>;                                                                 \
-    if (smem > 48 * 1024)                                                                                      \
-      DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));     \
+#define DDNN_SK_LAUNCH(KERN)                                                                                  \
+  do {                                                                                                        \
+    auto kern = KERN;                                                                                         \
+    if (smem > 48 * 1024)                                                                                     \
+      DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
     kern<<<(unsigned)blocks, 256, smem, st>>>((const TI*)X, (const TI*)W, bias, (TO*)A, B, (int)K, (int)N, act); \
   } while (0)
-  switch (nv4_of(N)) {
-    case 1: DDNN_SK_FWD(1); break;
-    case 2: DDNN_SK_FWD(2); break;
-    case 3: DDNN_SK_FWD(3); break;
-    default: DDNN_SK_FWD(4); break;
+  const int nv = nv4_of(N);
+  if (vec) {
+    const bool small = K / E <= 4 * 4;  // <= 4 chunks per lane: keep the register footprint small
+    if (small) {
+      switch (nv) {
+        case 1: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<1, 4, TI, TO>)); break;
+        case 2: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<2, 4, TI, TO>)); break;
+        case 3: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<3, 4, TI, TO>)); break;
+        default: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<4, 4, TI, TO>)); break;
+      }
+    } else {
+      switch (nv) {
+        case 1: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<1, 8, TI, TO>)); break;
+        case 2: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<2, 8, TI, TO>)); break;
+        case 3: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<3, 8, TI, TO>)); break;
+        default: DDNN_SK_LAUNCH((skinny_fwd_vec_kernel<4, 8, TI, TO>)); break;
+      }
+    }
+  } else {
+    switch (nv) {
+      case 1: DDNN_SK_LAUNCH((skinny_fwd_kernel<1, TI, TO>)); break;
+      case 2: DDNN_SK_LAUNCH((skinny_fwd_kernel<2, TI, TO>)); break;
+      case 3: DDNN_SK_LAUNCH((skinny_fwd_kernel<3, TI, TO>)); break;
+      default: DDNN_SK_LAUNCH((skinny_fwd_kernel<4, TI, TO>)); break;
+    }
   }
-#undef DDNN_SK_FWD
+#undef DDNN_SK_LAUNCH
   count_launch();
   DDNN_LAUNCH_CHECK();
   return DDNN_OK;
@@ -197,7 +333,7 @@ template <typename T>
 static int skinny_dx_t(const void* dZ, const void* W, const void* Aprev, void* out, int64_t B, int64_t K, int64_t N,
                        int act, cudaStream_t st) {
   const int ktiles = cdiv(K, 256);
-  const int rpb = rows_per_block_for(B, ktiles);
+  const int rpb = ROWS_TILE;  // one shared-memory tile per CTA: B/32 CTAs keep enough loads in flight
   dim3 grid(cdiv(B, rpb), ktiles);
 #define DDNN_SK_DX(NV) \
   skinny_dx_kernel<NV, T><<<grid, 256, 0, st>>>((const T*)dZ, (const T*)W, (const T*)Aprev, (T*)out, B, (int)K, (int)N, act, rpb)
