@@ -397,7 +397,10 @@ def bench_pipeline(workload, steps, warmup, device, rank, world, barrier):
             params.append({"weights": w, "biases": torch.full((n,), 0.01, device=device), "activation": a})
     layer = Layer.from_params(params, dims[lo], container_name=f"stage{rank}", dtype=dtype, device=device,
                               input_activation=(acts[lo - 1] if lo > 0 else "linear"), is_output=(hi == n_layers))
-    stage = PipelineStage(layer, rank, world)
+    transport = os.environ.get("DDNN_TRANSPORT", "peer") if world > 1 else "nccl"
+    stage = PipelineStage(layer, rank, world, transport=transport)
+    reserve = int(os.environ.get("DDNN_SM_RESERVE", "0")) if world > 1 else 0
+    _lib.set_sm_reserve(reserve)
     gx = torch.Generator(device=device).manual_seed(0)
     x = torch.rand((rows, dims[0]), device=device, generator=gx).to(torch.bfloat16) if rank == 0 else None
     y = torch.randint(0, dims[-1], (rows,), device=device, generator=gx, dtype=torch.int32) if rank == world - 1 else None
@@ -407,7 +410,8 @@ def bench_pipeline(workload, steps, warmup, device, rank, world, barrier):
         stage.train_step(x, y, rows, micro, 0.01)
     ms = timed(step, steps, warmup, device, barrier)
     launches = (_lib.launch_count() - l0) // max(1, steps + warmup)
-    return {"workload": workload, "rows": rows, "micro_batches": micro, "ms_total": ms, "dims": dims,
+    _lib.set_sm_reserve(0)
+    return {"sm_reserve": reserve, "transport": transport, "workload": workload, "rows": rows, "micro_batches": micro, "ms_total": ms, "dims": dims,
             "launches_per_step": launches, "stages": world, "layers_here": hi - lo}
 
 
@@ -535,6 +539,7 @@ def main():
                 v = pr["rows"] * psteps / (pms / 1e3)
                 f = flops_per_sample(pr["dims"])
                 pipes.append({"workload": wl, "stages": world, "micro_batches": pr["micro_batches"],
+                              "sm_reserve": pr["sm_reserve"], "transport": pr["transport"],
                               "rows_per_step": pr["rows"], "steps": psteps, "ms_per_step": pms / psteps,
                               "value": v, "unit": "samples/s", "scaling": "strong", "tflops_total": v * f / 1e12,
                               "tensor_frac_of_measured_burst": v * f / 1e12 / (world * peaks["bf16_tflops"]),

@@ -26,6 +26,7 @@ SYMBOLS = {
     "ddnn_last_error": (C.c_char_p, []),
     "ddnn_activation_from_name": (C.c_int, [C.c_char_p]),
     "ddnn_set_engine": (C.c_int, [_i32]),
+    "ddnn_set_sm_reserve": (C.c_int, [_i32]),
     "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
     "ddnn_softmax_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp]),
     "ddnn_activate": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp]),
@@ -38,6 +39,10 @@ SYMBOLS = {
                                                     _i32, _vp]),
     "ddnn_cast_f32_to_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_cast_bf16_to_f32": (C.c_int, [_vp, _vp, _i64, _vp]),
+    "ddnn_ipc_export": (C.c_int, [_vp, _vp, C.POINTER(C.c_int64)]),
+    "ddnn_ipc_import": (C.c_int, [_vp, _i64, C.POINTER(C.c_void_p)]),
+    "ddnn_flag_write": (C.c_int, [_vp, _i32, _vp]),
+    "ddnn_flag_wait": (C.c_int, [_vp, _i32, _vp]),
     "ddnn_launch_count": (_i64, []),
 }
 
@@ -91,3 +96,7 @@ def launch_count() -> int:
 
 def set_engine(engine: int) -> None:
     check(lib.ddnn_set_engine(engine))
+
+
+def set_sm_reserve(sms: int) -> None:
+    check(lib.ddnn_set_sm_reserve(sms))

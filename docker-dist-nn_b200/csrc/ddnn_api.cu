@@ -74,6 +74,15 @@ int ddnn_set_engine(int engine) {
   return DDNN_OK;
 }
 
+int ddnn_set_sm_reserve(int sms) {
+  if (sms < 0 || sms > 64) {
+    set_error("ddnn_set_sm_reserve: %d is out of range [0, 64]", sms);
+    return DDNN_ERR_ARG;
+  }
+  umma_set_sm_reserve(sms);
+  return DDNN_OK;
+}
+
 int64_t ddnn_launch_count(void) { return (int64_t)g_launches.load(); }
 
 int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K, int64_t N,

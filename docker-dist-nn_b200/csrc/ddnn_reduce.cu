@@ -95,6 +95,55 @@ colsum_kernel(const T* __restrict__ dZ, float* __restrict__ part, int64_t B, int
   }
 }
 
+// bf16, N % 8 == 0: lane owns 8 consecutive columns (one 16-byte load per row), each warp keeps 8
+// row-loads in flight; 8 warps stride the rows of the split and are combined through shared memory.
+__global__ void __launch_bounds__(256)
+colsum_bf16x8_kernel(const bf16* __restrict__ dZ, float* __restrict__ part, int64_t B, int N, int np, int rlen) {
+  __shared__ float red[8][32][9];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + lane * 8;
+  const int z = blockIdx.y;
+  const int64_t r0 = (int64_t)z * rlen;
+  const int64_t r1 = min(B, r0 + rlen);
+  float s[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) s[e] = 0.f;
+  if (col < N) {
+    for (int64_t r = r0 + warp * 8; r < r1; r += 64) {
+      uint4 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        v[u] = make_uint4(0, 0, 0, 0);
+        if (r + u < r1) v[u] = *reinterpret_cast<const uint4*>(dZ + (r + u) * N + col);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v[u]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __bfloat1622float2(h[e]);
+          s[2 * e] += f.x;
+          s[2 * e + 1] += f.y;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) red[warp][lane][e] = s[e];
+  __syncthreads();
+  if (warp == 0 && col < N) {
+    float a[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) a[e] = red[0][lane][e];
+#pragma unroll
+    for (int w = 1; w < 8; ++w)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) a[e] += red[w][lane][e];
+    st4(part + (int64_t)z * np + col, make_float4(a[0], a[1], a[2], a[3]));
+    st4(part + (int64_t)z * np + col + 4, make_float4(a[4], a[5], a[6], a[7]));
+  }
+}
+
 template <typename T>
 bool vec_ok(const T* p, int64_t ld) {
   return p && (ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p) % (4 * sizeof(T))) == 0);
@@ -140,7 +189,7 @@ int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K,
 }
 
 int colsum_splits(int64_t B, int64_t N) {
-  long strips = cdiv(N, 128);
+  long strips = cdiv(N, 256);
   long want = (2 * 148 + strips - 1) / strips;
   long max_by_rows = B / 64;
   if (max_by_rows < 1) max_by_rows = 1;
@@ -156,6 +205,9 @@ int colsum_partials(const void* dZ, float* db_part, int splits, int64_t B, int64
   if (dtype == DDNN_F32) {
     colsum_kernel<float><<<grid, 256, 0, st>>>((const float*)dZ, db_part, B, (int)N, np, rlen,
                                                vec_ok((const float*)dZ, N));
+  } else if (dtype == DDNN_BF16 && N % 8 == 0 && reinterpret_cast<uintptr_t>(dZ) % 16 == 0) {
+    dim3 grid8(cdiv(N, 256), splits);
+    colsum_bf16x8_kernel<<<grid8, 256, 0, st>>>((const bf16*)dZ, db_part, B, (int)N, np, rlen);
   } else if (dtype == DDNN_BF16) {
     colsum_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)dZ, db_part, B, (int)N, np, rlen,
                                               vec_ok((const bf16*)dZ, N));

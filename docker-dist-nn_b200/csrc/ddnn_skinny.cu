@@ -180,13 +180,13 @@ skinny_dx_kernel(const T* __restrict__ dZ, const T* __restrict__ W, const T* __r
     __syncthreads();
     if (k < K) {
 #pragma unroll
-      for (int rg = 0; rg < ROWS_TILE; rg += 8) {
-        float a8[8];  // the 8 A_prev loads of this group are issued before the first use
+      for (int rg = 0; rg < ROWS_TILE; rg += 16) {
+        float a8[16];  // the 16 A_prev loads of this group are issued before the first use
 #pragma unroll
-        for (int u = 0; u < 8; ++u)
+        for (int u = 0; u < 16; ++u)
           a8[u] = (act != DDNN_ACT_LINEAR && rg + u < nr) ? ld1(Aprev + (rb + rg + u) * K + k) : 1.f;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
           if (rg + u < nr) {
             float acc = 0.f;
 #pragma unroll
@@ -231,12 +231,12 @@ skinny_dw_kernel(const T* __restrict__ X, const T* __restrict__ dZ, float* __res
       for (int r = 0; r < nr; ++r) dbs += dzs[r][threadIdx.x];
     if (k < K) {
 #pragma unroll
-      for (int rg = 0; rg < ROWS_TILE; rg += 8) {
-        float x8[8];  // 8 independent loads in flight before the FMAs (rows past nr contribute x = 0)
+      for (int rg = 0; rg < ROWS_TILE; rg += 16) {
+        float x8[16];  // 16 independent loads in flight before the FMAs (rows past nr contribute x = 0)
 #pragma unroll
-        for (int u = 0; u < 8; ++u) x8[u] = rg + u < nr ? ld1(X + (rb + rg + u) * K + k) : 0.f;
+        for (int u = 0; u < 16; ++u) x8[u] = rg + u < nr ? ld1(X + (rb + rg + u) * K + k) : 0.f;
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
+        for (int u = 0; u < 16; ++u) {
 #pragma unroll
           for (int q = 0; q < NV4; ++q) {
             const float4 d = *reinterpret_cast<const float4*>(&dzs[rg + u][4 * q]);
@@ -321,8 +321,8 @@ int skinny_forward(const void* X, const void* W, const float* bias, void* A, int
 }
 
 static int rows_per_block_for(int64_t B, int ktiles) {
-  // >= 2 waves of CTAs, whole shared-memory tiles per block
-  long want_blocks = (2 * 148 + ktiles - 1) / ktiles;
+  // >= 4 CTAs per SM (enough loads in flight to cover HBM latency), whole shared-memory tiles per block
+  long want_blocks = (4 * 148 + ktiles - 1) / ktiles;
   long rpb = (B + want_blocks - 1) / want_blocks;
   rpb = ((rpb + ROWS_TILE - 1) / ROWS_TILE) * ROWS_TILE;
   if (rpb < ROWS_TILE) rpb = ROWS_TILE;

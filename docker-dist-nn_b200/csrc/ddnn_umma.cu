@@ -480,6 +480,8 @@ int get_tmap(const bf16* ptr, uint64_t inner, uint64_t outer, uint32_t b0, uint3
   return DDNN_OK;
 }
 
+std::atomic<int> g_sm_reserve{0};
+
 int num_sms() {
   static int n = 0;
   if (n == 0) {
@@ -502,7 +504,9 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p
     attr_set = true;
   }
   const int total = p.m_blocks * p.n_blocks * p.splits;
-  const int grid = total < num_sms() ? total : num_sms();
+  int ctas = num_sms() - g_sm_reserve.load();
+  if (ctas < 1) ctas = 1;
+  const int grid = total < ctas ? total : ctas;
   kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, st>>>(ta, tb, p);
   count_launch();
   DDNN_LAUNCH_CHECK();
@@ -541,6 +545,8 @@ void fill_tiles(UmmaParams& p, int64_t M, int64_t N, int64_t Kred, int bn, int s
 }
 
 }  // namespace
+
+void umma_set_sm_reserve(int sms) { g_sm_reserve.store(sms < 0 ? 0 : sms); }
 
 bool umma_shape_ok(int64_t B, int64_t K, int64_t N) { return B > 0 && K >= 8 && N >= 8 && K % 8 == 0 && N % 8 == 0; }
 

@@ -238,10 +238,14 @@ class Layer:
     def output_buffer(self, row0: int, rows: int) -> torch.Tensor:
         return self._bufs["a"][-1][row0:row0 + rows]
 
-    def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None) -> torch.Tensor:
+    def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None,
+                      out_target: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Forward of rows [row0, row0+rows) keeping what backward needs.  ``x`` None means the
         rows are already in ``input_buffer``.  An output node stops at the fp32 logits Z
-        (softmax is fused into ``loss_and_grad``)."""
+        (softmax is fused into ``loss_and_grad``).  ``out_target`` (rows, N_last) redirects the
+        LAST local layer's output, e.g. to the next stage's input buffer mapped from a peer GPU:
+        the GEMM epilogue then stores over NVLink and no local copy of that activation exists
+        (this node never reads its own last output)."""
         a = self._bufs["a"]
         if x is not None:
             rows = x.shape[0]
@@ -264,9 +268,10 @@ class Layer:
             elif act == "softmax":
                 raise ValueError("hidden softmax layers are not supported in training (row Jacobian)")
             k_, n_ = p["weights"].shape
+            dst = out_target if (last and out_target is not None) else a[i + 1][row0:row0 + rows]
             with self._span(f"forward L{i + 1} {k_}->{n_}"):
-                ops.dense_forward(a[i][row0:row0 + rows], self._w(i), p["biases"], act, out=a[i + 1][row0:row0 + rows])
-        return a[-1][row0:row0 + rows]
+                ops.dense_forward(a[i][row0:row0 + rows], self._w(i), p["biases"], act, out=dst)
+        return out_target if out_target is not None else a[-1][row0:row0 + rows]
 
     def loss_and_grad(self, labels: torch.Tensor, row0: int = 0, denom: Optional[int] = None,
                       accumulate: bool = False) -> torch.Tensor:
@@ -283,8 +288,8 @@ class Layer:
                            b["row_loss"][row0:row0 + rows], b["loss"], 1.0 / float(denom), accumulate=accumulate)
         return b["loss"]
 
-    def backward(self, row0: int = 0, rows: Optional[int] = None, need_input_grad: bool = True
-                 ) -> Optional[torch.Tensor]:
+    def backward(self, row0: int = 0, rows: Optional[int] = None, need_input_grad: bool = True,
+                 dx_target: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
         """dX chain for rows [row0, row0+rows): dZ[l-1] = (dZ[l].W_l^T) * f'_{l-1}(A[l]).  Returns
         dZ for the node feeding this one (already multiplied by that node's activation
         derivative, ``input_activation``) or None when ``need_input_grad`` is False."""
@@ -299,9 +304,10 @@ class Layer:
         if not need_input_grad:
             return None
         k_, n_ = self.layer_params[0]["weights"].shape
+        dst = dx_target if dx_target is not None else b["dx"][sl]  # dx_target: the upstream stage's dZ buffer (peer)
         with self._span(f"dX L1 {n_}->{k_}"):
-            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), b["a"][0][sl], self.input_activation, out=b["dx"][sl])
-        return b["dx"][sl]
+            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), b["a"][0][sl], self.input_activation, out=dst)
+        return dst
 
     def step(self, lr: float, rows: Optional[int] = None) -> None:
         """dW = A^T.dZ over the first ``rows`` buffered rows with the SGD update fused into the

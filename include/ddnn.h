@@ -146,6 +146,28 @@ int ddnn_dense_backward_dw_sgd_static(const void* X, const void* dZ,
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
 
+/* Leaves `sms` SMs free of the persistent tcgen05 GEMM CTAs (default 0).  The pipeline sets this
+ * so that NCCL's send/recv kernels, which cannot co-reside with a 210 KB-shared-memory GEMM CTA,
+ * always find an SM and run beside the GEMM instead of between GEMMs.  No reference counterpart. */
+int ddnn_set_sm_reserve(int sms);
+
+/*
+ * Peer-memory transport of the layer-per-GPU pipeline (replaces the gRPC hop of
+ * /root/reference/src/grpc_node.py:120-135; no reference counterpart as an API).
+ * ddnn_ipc_export : CUDA-IPC handle (64 bytes) of the allocation containing `ptr` + ptr's offset
+ *                   in it; the bytes are sent to the neighbour process by any host channel.
+ * ddnn_ipc_import : maps that allocation into this process (once per handle) and returns the
+ *                   peer pointer.  It is a normal device pointer for every entry point above: give
+ *                   it as the OUTPUT of ddnn_dense_forward / ddnn_dense_backward_dx and the GEMM
+ *                   epilogue stores straight into the neighbour GPU's memory over NVLink.
+ * ddnn_flag_write : stream-ordered 4-byte store (after a system-scope fence) to a local or peer flag.
+ * ddnn_flag_wait  : makes `stream` wait until *flag >= value (cuStreamWaitValue32; flag is local).
+ */
+int ddnn_ipc_export(const void* ptr, void* handle64, int64_t* offset);
+int ddnn_ipc_import(const void* handle64, int64_t offset, void** ptr);
+int ddnn_flag_write(int32_t* flag, int32_t value, void* stream);
+int ddnn_flag_wait(const int32_t* flag, int32_t value, void* stream);
+
 /* Count of kernels this library has launched in this process (bench.py gpu_launches). */
 int64_t ddnn_launch_count(void);
 
