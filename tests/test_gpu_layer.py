@@ -209,3 +209,42 @@ def test_two_stage_chain_equals_single_node(cuda_device):
     for a, b in zip(single.export_params(), chained):
         assert rel_err(b["weights"], a["weights"]) < 1e-6
         assert rel_err(b["biases"], a["biases"]) < 1e-6
+
+
+def test_direct_output_targets_and_flags(cuda_device):
+    """What the peer transport does, on one GPU and ONE stream (so every flag is already set when its
+    wait executes -- two streams waiting on each other on one GPU may share a hardware queue and
+    deadlock): stage 0's forward epilogue writes straight into stage 1's input buffer (out_target),
+    stage 1's dX epilogue writes into stage 0's gradient buffer (dx_target), ddnn_flag_write /
+    ddnn_flag_wait bracket every hand-over.  Result must equal the single-node step bit for bit."""
+    from ddnn_b200 import Layer, Trainer, _lib
+    dims, acts = [64, 48, 40, 10], ["relu", "sigmoid", "softmax"]
+    x, y = synthetic_batch(96, 64, 10, seed=6)
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    single = Trainer(make_params(dims, acts, seed=4))
+    single.train_step(xd, yd, 0.1)
+    p = make_params(dims, acts, seed=4)
+    s0 = Layer.from_params(p[:2], 64, is_output=False)
+    s1 = Layer.from_params(p[2:], 40, is_output=True, input_activation="sigmoid")
+    s0.begin_batch(96); s1.begin_batch(96)
+    flags = torch.zeros(8, dtype=torch.int32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    fw = lambda i, v: _lib.check(_lib.lib.ddnn_flag_write(flags.data_ptr() + 4 * i, v, st))  # noqa: E731
+    fwait = lambda i, v: _lib.check(_lib.lib.ddnn_flag_wait(flags.data_ptr() + 4 * i, v, st))  # noqa: E731
+    chunks = [(0, 32), (32, 64), (64, 96)]
+    for m, (r0, r1) in enumerate(chunks):
+        s0.forward_train(xd[r0:r1], r0, out_target=s1.input_buffer(r0, r1 - r0))
+        fw(m, 1)
+        fwait(m, 1)
+        s1.forward_train(None, r0, r1 - r0)
+    for m, (r0, r1) in enumerate(chunks):
+        s1.loss_and_grad(yd[r0:r1], r0, denom=96, accumulate=m > 0)
+        s1.backward(r0, r1 - r0, dx_target=s0.grad_buffer(r0, r1 - r0))
+        fw(4 + m, 2)
+        fwait(4 + m, 1)   # GEQ: 2 >= 1
+        s0.backward(r0, r1 - r0, need_input_grad=False)
+    s0.step(0.1); s1.step(0.1)
+    torch.cuda.synchronize()
+    assert flags.tolist() == [1, 1, 1, 0, 2, 2, 2, 0]
+    for a, b in zip(single.export_params(), s0.export_params() + s1.export_params()):
+        assert np.array_equal(a["weights"], b["weights"]) and np.array_equal(a["biases"], b["biases"])

@@ -40,7 +40,8 @@ def main():
     dist.init_process_group("nccl", timeout=datetime.timedelta(seconds=120))
     ok = True
     for dims, acts, dtype, rows, micro in [([512] * 5, ["relu", "sigmoid", "relu", "softmax"], "bf16", 2048, 4),
-                                           ([64, 48, 40, 32, 10], ["relu", "relu", "sigmoid", "softmax"], "f32", 300, 3)]:
+                                           ([64, 48, 40, 32, 10], ["relu", "relu", "sigmoid", "softmax"], "f32", 300, 3),
+                                           ([256] * 9, ["relu", "sigmoid"] * 3 + ["relu", "softmax"], "bf16", 1024, 5)]:
         if world > len(acts):
             continue
         w_n, l_n, (lo, hi) = run("nccl", dims, acts, dtype, rows, micro, 4, rank, world, device)
