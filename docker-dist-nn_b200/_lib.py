@@ -27,6 +27,7 @@ SYMBOLS = {
     "ddnn_activation_from_name": (C.c_int, [C.c_char_p]),
     "ddnn_set_engine": (C.c_int, [_i32]),
     "ddnn_set_sm_reserve": (C.c_int, [_i32]),
+    "ddnn_set_f32_tensor_cores": (C.c_int, [_i32]),
     "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
     "ddnn_softmax_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp]),
     "ddnn_activate": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp]),
@@ -96,6 +97,10 @@ def launch_count() -> int:
 
 def set_engine(engine: int) -> None:
     check(lib.ddnn_set_engine(engine))
+
+
+def set_f32_tensor_cores(on: bool) -> None:
+    check(lib.ddnn_set_f32_tensor_cores(1 if on else 0))
 
 
 def set_sm_reserve(sms: int) -> None:

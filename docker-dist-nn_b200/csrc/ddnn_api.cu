@@ -74,6 +74,11 @@ int ddnn_set_engine(int engine) {
   return DDNN_OK;
 }
 
+int ddnn_set_f32_tensor_cores(int on) {
+  simt_set_f32_core(on);
+  return DDNN_OK;
+}
+
 int ddnn_set_sm_reserve(int sms) {
   if (sms < 0 || sms > 64) {
     set_error("ddnn_set_sm_reserve: %d is out of range [0, 64]", sms);

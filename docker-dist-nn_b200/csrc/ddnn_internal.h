@@ -13,6 +13,7 @@ int simt_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev, int6
 int simt_dw_partials(const void* X, const void* dZ, float* dw_part, float* db_part, int splits,
                      int64_t B, int64_t K, int64_t N, int dtype, cudaStream_t st);
 int simt_dw_splits(int64_t B, int64_t K, int64_t N);
+void simt_set_f32_core(int tensor);  // 1: 3xTF32 mma inner product (default), 0: FFMA
 
 // ---- skinny output layers, N <= 16 (ddnn_skinny.cu) ------------------------------------
 bool skinny_ok(int64_t K, int64_t N);

@@ -146,6 +146,10 @@ int ddnn_dense_backward_dw_sgd_static(const void* X, const void* dZ,
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
 
+/* fp32 path inner product for aligned forward / dW GEMMs: 0 (default) = FFMA, 1 = error-compensated
+ * 3xTF32 on the tensor cores (still within the 1e-5 bound; ~4x the FFMA rounding error). */
+int ddnn_set_f32_tensor_cores(int on);
+
 /* Leaves `sms` SMs free of the persistent tcgen05 GEMM CTAs (default 0).  The pipeline sets this
  * so that NCCL's send/recv kernels, which cannot co-reside with a 210 KB-shared-memory GEMM CTA,
  * always find an SM and run beside the GEMM instead of between GEMMs.  No reference counterpart. */

@@ -210,3 +210,24 @@ def test_skinny_output_layer_kernels(cuda_device, bkn, dt):
     dx = ops.dense_backward_dx(dzd, wd, ad, "relu")
     ref = np.dot(dzr, wr.T) * (ar > 0)
     assert rel_err(to_np(dx), ref) < (F32_TOL if dt == "f32" else 6e-3)
+
+
+@pytest.mark.parametrize("shape", [(4096, 784, 128), (333, 128, 64), (4096, 64, 128), (1000, 100, 132)])
+@pytest.mark.parametrize("tensor_cores", [True, False])
+def test_f32_inner_product_cores(cuda_device, shape, tensor_cores):
+    """fp32 forward and dW on 16-byte-aligned shapes: the FFMA inner product (default) and the opt-in
+    error-compensated 3xTF32 tensor-core one must both stay within the fp32 bound of the float64 oracle."""
+    from ddnn_b200 import _lib, ops
+    b, k, n = shape
+    x, w, bias = _data(b, k, n, seed=12)
+    rng = np.random.default_rng(13)
+    dz = rng.standard_normal((b, n)) / b
+    _lib.set_f32_tensor_cores(tensor_cores)
+    try:
+        got = ops.dense_forward(to_dev(x), to_dev(w), to_dev(bias), "relu")
+        assert rel_err(to_np(got), oracle.activate(np.dot(x, w) + bias, "relu")) < F32_TOL
+        dw, db = ops.dense_backward_dw(to_dev(x), to_dev(dz))
+        assert rel_err(to_np(dw), np.dot(x.T, dz)) < F32_TOL
+        assert rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+    finally:
+        _lib.set_f32_tensor_cores(False)
