@@ -28,6 +28,7 @@ SYMBOLS = {
     "ddnn_set_engine": (C.c_int, [_i32]),
     "ddnn_set_sm_reserve": (C.c_int, [_i32]),
     "ddnn_set_f32_tensor_cores": (C.c_int, [_i32]),
+    "ddnn_set_cta_pairs": (C.c_int, [_i32]),
     "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
     "ddnn_softmax_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp]),
     "ddnn_activate": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp]),
@@ -97,6 +98,10 @@ def launch_count() -> int:
 
 def set_engine(engine: int) -> None:
     check(lib.ddnn_set_engine(engine))
+
+
+def set_cta_pairs(on: bool) -> None:
+    check(lib.ddnn_set_cta_pairs(1 if on else 0))
 
 
 def set_f32_tensor_cores(on: bool) -> None:

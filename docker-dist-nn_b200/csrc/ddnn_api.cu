@@ -74,6 +74,11 @@ int ddnn_set_engine(int engine) {
   return DDNN_OK;
 }
 
+int ddnn_set_cta_pairs(int on) {
+  umma_set_pair(on);
+  return DDNN_OK;
+}
+
 int ddnn_set_f32_tensor_cores(int on) {
   simt_set_f32_core(on);
   return DDNN_OK;

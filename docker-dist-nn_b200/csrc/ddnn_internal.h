@@ -47,6 +47,7 @@ int cast_bf16_f32(const bf16* in, float* out, int64_t n, cudaStream_t st);
 // ---- tcgen05 / TMA / TMEM GEMMs (ddnn_umma.cu) ----------------------------------------
 bool umma_shape_ok(int64_t B, int64_t K, int64_t N);
 void umma_set_sm_reserve(int sms);
+void umma_set_pair(int on);  // 1: CTA-pair (cta_group::2) kernel where it applies (default)
 int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64_t B, int64_t K,
                  int64_t N, int act, int out_dtype, cudaStream_t st);
 int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int64_t B, int64_t K,

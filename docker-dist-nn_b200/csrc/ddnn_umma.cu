@@ -122,6 +122,64 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---- cta_group::2 (CTA pair) wrappers -------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load executed by either CTA of the pair; the transaction bytes are credited to the barrier at the
+// same offset in CTA 0 (peer bit 24 of the shared::cluster address cleared).
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+          "r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish_pair() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+// D[tmem of both CTAs] (+)= A . B with M = 256 over the pair; issued by ONE thread of CTA 0
+__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                               uint32_t accum) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+// arrives (once all previously issued MMAs of this thread are done) on the barrier at this offset in BOTH CTAs
+__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
+      "h"((uint16_t)3)
+      : "memory");
+}
+// arrive on the barrier at the same offset in CTA `rank` of the cluster
+__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 ra;\n"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n"
+      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "}\n" ::"r"(bar),
+      "r"(rank)
+      : "memory");
+}
+
 // ---- descriptors --------------------------------------------------------------------
 // Shared-memory matrix descriptor (sm_100): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) |
 // version=1 [46,48) | layout [61,64) (2 = SWIZZLE_128B).
@@ -181,6 +239,104 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, const UmmaParams& p) 
   t.kb0 = t.ks * p.kb_per_split;
   t.kb1 = min(p.num_kb, t.kb0 + p.kb_per_split);
   return t;
+}
+
+// Epilogue of one 128 x BN accumulator tile for the warp owning TMEM lanes [32q, 32q+32).
+// row0 = first output row of this warp, n0 = first output column of the tile.
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, uint32_t tmem_acc, int row0, int n0,
+                                              int64_t zoff, int q, int lane) {
+  // Each thread holds one accumulator ROW (TMEM lane) x 32 columns.  A 32x32 transpose through
+  // shared memory regroups that as lane = (row r8 = lane/4, 8 consecutive columns cg = lane%4): one
+  // warp instruction then touches 8 rows x 64 B (bf16) / 128 B (fp32) contiguous per row, every
+  // global access is a 16-byte vector, and a lane issues its 4 row-loads (A_prev / W) together.
+  const int nrows = min(32, p.M - row0);  // warp-uniform
+  const int cg = lane & 3, r8 = lane >> 2;
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; ++c) {
+    float v[32];
+    tmem_ld32(tmem_acc + c * 32 + ((uint32_t)(q * 32) << 16), v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(&stg[lane * Cfg<BN>::STG_PITCH + 4 * j]) =
+          make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncwarp();
+    const int col = n0 + c * 32 + cg * 8;  // N % 8 == 0: a group of 8 columns is all in or all out
+    if (col < p.N) {
+      const int64_t idx0 = ((int64_t)row0 + zoff) * p.N + col;
+      float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+      if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+        b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+      }
+      uint4 ap[4];         // EPI_DX: 8 bf16 of A_prev per row
+      float4 w0[4], w1[4];  // EPI_SGD: 8 fp32 of W_master per row
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int r = it * 8 + r8;
+        if (EPI == EPI_DX) {
+          ap[it] = make_uint4(0, 0, 0, 0);
+          if (p.act != DDNN_ACT_LINEAR && r < nrows)
+            ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
+        }
+        if (EPI == EPI_SGD) {
+          w0[it] = w1[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (r < nrows) {
+            w0[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N);
+            w1[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N + 4);
+          }
+        }
+      }
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int r = it * 8 + r8;
+        if (r >= nrows) continue;
+        const float4 x0 = *reinterpret_cast<const float4*>(&stg[r * Cfg<BN>::STG_PITCH + cg * 8]);
+        const float4 x1 = *reinterpret_cast<const float4*>(&stg[r * Cfg<BN>::STG_PITCH + cg * 8 + 4]);
+        float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+        const int64_t idx = idx0 + (int64_t)r * p.N;
+        if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) x[e] = act_fwd(x[e] + bb[e], p.act);
+        } else if (EPI == EPI_DX) {
+          if (p.act != DDNN_ACT_LINEAR) {
+            const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&ap[it]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 a = __bfloat1622float2(a2[e]);
+              x[2 * e] *= act_bwd(a.x, p.act);
+              x[2 * e + 1] *= act_bwd(a.y, p.act);
+            }
+          }
+        } else if (EPI == EPI_SGD) {
+          const float ww[8] = {w0[it].x, w0[it].y, w0[it].z, w0[it].w, w1[it].x, w1[it].y, w1[it].z, w1[it].w};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) x[e] = ww[e] - p.lr * x[e];
+        }
+        if (EPI == EPI_FWD_BF16 || EPI == EPI_DX) {
+          uint4 o;
+          __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+          *reinterpret_cast<uint4*>((bf16*)p.out + idx) = o;
+        } else {
+          float* dst = EPI == EPI_SGD ? p.w_master + idx : (float*)p.out + idx;
+          *reinterpret_cast<float4*>(dst) = make_float4(x[0], x[1], x[2], x[3]);
+          *reinterpret_cast<float4*>(dst + 4) = make_float4(x[4], x[5], x[6], x[7]);
+          if (EPI == EPI_SGD && p.w_shadow) {
+            uint4 o;
+            __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+            *reinterpret_cast<uint4*>(p.w_shadow + idx) = o;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  }
 }
 
 template <bool A_MN, bool B_MN, int BN, int EPI>
@@ -295,99 +451,8 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const TileCoord t = decode_tile(tile, p);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
-      // Each thread holds one accumulator ROW (TMEM lane) x 32 columns.  A 32x32 transpose through
-      // shared memory regroups that as lane = (row r8 = lane/4, 8 consecutive columns cg = lane%4): one
-      // warp instruction then touches 8 rows x 64 B (bf16) / 128 B (fp32) contiguous per row, every
-      // global access is a 16-byte vector, and a lane issues its 4 row-loads (A_prev / W) together.
-      const int row0 = t.m_blk * BLOCK_M + q * 32;
-      const int nrows = min(32, p.M - row0);  // warp-uniform
-      const int64_t zoff = EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0;
-      const int cg = lane & 3, r8 = lane >> 2;
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        float v[32];
-        tmem_ld32(tmem_base + as * BN + c * 32 + ((uint32_t)(q * 32) << 16), v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(&stg[lane * C::STG_PITCH + 4 * j]) =
-              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-        __syncwarp();
-        const int col = t.n_blk * BN + c * 32 + cg * 8;  // N % 8 == 0: a group of 8 columns is all in or all out
-        if (col < p.N) {
-          const int64_t idx0 = ((int64_t)row0 + zoff) * p.N + col;
-          float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-          if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
-            b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-            b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-          }
-          uint4 ap[4];         // EPI_DX: 8 bf16 of A_prev per row
-          float4 w0[4], w1[4];  // EPI_SGD: 8 fp32 of W_master per row
-#pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int r = it * 8 + r8;
-            if (EPI == EPI_DX) {
-              ap[it] = make_uint4(0, 0, 0, 0);
-              if (p.act != DDNN_ACT_LINEAR && r < nrows)
-                ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
-            }
-            if (EPI == EPI_SGD) {
-              w0[it] = w1[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (r < nrows) {
-                w0[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N);
-                w1[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N + 4);
-              }
-            }
-          }
-#pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int r = it * 8 + r8;
-            if (r >= nrows) continue;
-            const float4 x0 = *reinterpret_cast<const float4*>(&stg[r * C::STG_PITCH + cg * 8]);
-            const float4 x1 = *reinterpret_cast<const float4*>(&stg[r * C::STG_PITCH + cg * 8 + 4]);
-            float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-            const int64_t idx = idx0 + (int64_t)r * p.N;
-            if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
-              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-              for (int e = 0; e < 8; ++e) x[e] = act_fwd(x[e] + bb[e], p.act);
-            } else if (EPI == EPI_DX) {
-              if (p.act != DDNN_ACT_LINEAR) {
-                const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&ap[it]);
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const float2 a = __bfloat1622float2(a2[e]);
-                  x[2 * e] *= act_bwd(a.x, p.act);
-                  x[2 * e + 1] *= act_bwd(a.y, p.act);
-                }
-              }
-            } else if (EPI == EPI_SGD) {
-              const float ww[8] = {w0[it].x, w0[it].y, w0[it].z, w0[it].w, w1[it].x, w1[it].y, w1[it].z, w1[it].w};
-#pragma unroll
-              for (int e = 0; e < 8; ++e) x[e] = ww[e] - p.lr * x[e];
-            }
-            if (EPI == EPI_FWD_BF16 || EPI == EPI_DX) {
-              uint4 o;
-              __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
-              *reinterpret_cast<uint4*>((bf16*)p.out + idx) = o;
-            } else {
-              float* dst = EPI == EPI_SGD ? p.w_master + idx : (float*)p.out + idx;
-              *reinterpret_cast<float4*>(dst) = make_float4(x[0], x[1], x[2], x[3]);
-              *reinterpret_cast<float4*>(dst + 4) = make_float4(x[4], x[5], x[6], x[7]);
-              if (EPI == EPI_SGD && p.w_shadow) {
-                uint4 o;
-                __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-                for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
-                *reinterpret_cast<uint4*>(p.w_shadow + idx) = o;
-              }
-            }
-          }
-        }
-        __syncwarp();
-      }
+      epilogue_tile<BN, EPI>(p, stg, tmem_base + as * BN, t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
+                             EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0, q, lane);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(as));
@@ -401,6 +466,161 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ===================== CTA-pair kernel: 256 x 256 tile per 2-CTA cluster =====================
+// tcgen05.mma.cta_group::2 with M = 256: each CTA of the pair stages its own 128 rows of A and HALF of the
+// B tile (128 of the 256 N columns), so a CTA moves 32 KB per k-block instead of 48 KB (one third less
+// L2 -> SM traffic and shared-memory fill per FLOP) and the ring holds 6 stages instead of 4.  CTA 0
+// issues the MMAs for the pair; every CTA keeps the 128 x 256 accumulator of its own rows in its own
+// TMEM and runs its own epilogue.  Barriers: full[s] lives in CTA 0 and collects the TMA bytes of both
+// CTAs; tcgen05.commit multicasts the "stage free" and "accumulator ready" arrivals to both CTAs; CTA 1's
+// epilogue warps arrive remotely on CTA 0's "accumulator drained" barrier.
+struct Cfg2 {
+  static constexpr int BN = 256;
+  static constexpr int STAGES = 6;
+  static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;      // 128 rows of A per CTA
+  static constexpr uint32_t B_BYTES = (BN / 2) * BLOCK_K * 2;     // 128 of the 256 B columns per CTA
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;      // 32 KB
+  static constexpr uint32_t TMEM_COLS = 2 * BN;
+  static constexpr uint32_t BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
+  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + Cfg<256>::STG_BYTES;
+};
+
+template <bool A_MN, bool B_MN, int EPI>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                      const UmmaParams p) {
+  using C = Cfg2;
+  constexpr int BN = C::BN;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  const uint32_t bars = tiles + C::STAGES * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };
+  auto tfull_bar = [&](int a) { return bars + 8u * (2 * C::STAGES + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (2 * C::STAGES + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (2 * C::STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();  // 0 = leader (issues the MMAs)
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+  // p.m_blocks counts 256-row blocks here
+  const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);   // used in CTA 0 only: one arrive.expect_tx + the bytes of both CTAs
+      mbar_init(empty_bar(s), 1);  // one multicast commit
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);   // one multicast commit
+      mbar_init(tempty_bar(a), 8);  // used in CTA 0 only: 4 epilogue warps of each CTA
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc_pair(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish_pair();
+  }
+  tc_fence_before();
+  cluster_sync_all();  // both CTAs' barriers and TMEM exist before anything crosses the pair
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        const TileCoord t = decode_tile(tile, p);
+        const int m_row = t.m_blk * 256 + (int)rank * BLOCK_M;   // this CTA's 128 rows of the 256-row tile
+        const int n_col = t.n_blk * BN + (int)rank * (BN / 2);   // this CTA's half of the B tile
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          if (rank == 0) mbar_expect_tx(full_bar(stage), 2 * C::STAGE_BYTES);
+          const uint32_t a_dst = tiles + stage * C::STAGE_BYTES;
+          const uint32_t b_dst = a_dst + C::A_BYTES;
+          if (!A_MN) {
+            tma_load_2d_pair(a_dst, &tma_a, full_bar(stage), kb * BLOCK_K, m_row);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BLOCK_M / 64; ++i)
+              tma_load_2d_pair(a_dst + i * (BLOCK_K * 128), &tma_a, full_bar(stage), m_row + i * 64, kb * BLOCK_K);
+          }
+          if (!B_MN) {
+            tma_load_2d_pair(b_dst, &tma_b, full_bar(stage), kb * BLOCK_K, n_col);
+          } else {
+#pragma unroll
+            for (int i = 0; i < (BN / 2) / 64; ++i)
+              tma_load_2d_pair(b_dst + i * (BLOCK_K * 128), &tma_b, full_bar(stage), n_col + i * 64, kb * BLOCK_K);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA only) =====================
+    if (rank == 0 && lane == 0) {
+      // M = 256 over the pair, N = 256
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((A_MN ? 1u : 0u) << 15) |
+                                 ((B_MN ? 1u : 0u) << 16) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+        const TileCoord t = decode_tile(tile, p);
+        mbar_wait(tempty_bar(as), aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + as * BN;
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t a_base = tiles + stage * C::STAGE_BYTES;
+          const uint32_t b_base = a_base + C::A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_bf16_pair(d_tmem, operand_desc<A_MN>(a_base, k), operand_desc<B_MN>(b_base, k), idesc,
+                           (kb > t.kb0 || k > 0) ? 1u : 0u);
+          umma_commit_pair(empty_bar(stage));
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_pair(tfull_bar(as));
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue (both CTAs, own 128 rows) =====================
+    const int q = warp & 3;
+    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * 32 * Cfg<256>::STG_PITCH;
+    uint32_t as = 0, aphase = 0;
+    for (int tile = pair; tile < total_tiles; tile += num_pairs) {
+      const TileCoord t = decode_tile(tile, p);
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      epilogue_tile<BN, EPI>(p, stg, tmem_base + as * BN, t.m_blk * 256 + (int)rank * BLOCK_M + q * 32, t.n_blk * BN,
+                             EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0, q, lane);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_remote(tempty_bar(as), 0);
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  cluster_sync_all();  // the leader must not read the peer's shared memory after the peer has left
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_pair(tmem_base, C::TMEM_COLS);
   }
 }
 
@@ -513,6 +733,48 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p
   return DDNN_OK;
 }
 
+std::atomic<int> g_use_pair{1};  // 1: CTA-pair (cta_group::2) kernel for large BN = 256 problems
+
+template <bool A_MN, bool B_MN, int EPI>
+int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cudaStream_t st) {
+  auto kern = umma_pair_gemm_kernel<A_MN, B_MN, EPI>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM_BYTES));
+    attr_set = true;
+  }
+  // tile space in 256-row blocks; rasterisation group halves accordingly
+  p.m_blocks = cdiv(p.M, 256);
+  p.group_m = p.group_m > 1 ? (p.group_m + 1) / 2 : 1;
+  if (p.group_m > p.m_blocks) p.group_m = p.m_blocks;
+  const int total = p.m_blocks * p.n_blocks * p.splits;
+  int pairs = (num_sms() - g_sm_reserve.load()) / 2;
+  if (pairs < 1) pairs = 1;
+  if (pairs > total) pairs = total;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(2 * pairs);
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = Cfg2::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+  count_launch();
+  return DDNN_OK;
+}
+
+// the pair kernel pays off when there are at least two waves of 256x256 tiles and no split-K
+bool pair_ok(int bn, const UmmaParams& p) {
+  if (!g_use_pair.load() || bn != 256 || p.splits != 1) return false;
+  const long tiles = (long)cdiv(p.M, 256) * p.n_blocks;
+  return tiles >= 2 * (num_sms() / 2);
+}
+
 template <bool A_MN, bool B_MN, int EPI>
 int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p, cudaStream_t st) {
   if (bn == 256) return launch_one<A_MN, B_MN, 256, EPI>(ta, tb, p, st);
@@ -522,10 +784,11 @@ int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const UmmaPa
 
 // A operand map: K-major -> stored [M][Kred], box {64, 128}; MN-major -> stored [Kred][M], box {64, 64}
 int operand_maps(bool a_mn, const bf16* A, bool b_mn, const bf16* Bm, int64_t M, int64_t N, int64_t Kred, int bn,
-                 CUtensorMap* ta, CUtensorMap* tb) {
+                 CUtensorMap* ta, CUtensorMap* tb, bool pair = false) {
   int rc = a_mn ? get_tmap(A, M, Kred, 64, 64, ta) : get_tmap(A, Kred, M, 64, BLOCK_M, ta);
   if (rc != DDNN_OK) return rc;
-  return b_mn ? get_tmap(Bm, N, Kred, 64, 64, tb) : get_tmap(Bm, Kred, N, 64, bn, tb);
+  // K-major B: one box of bn rows (a CTA of a pair loads only its half: bn / 2 rows)
+  return b_mn ? get_tmap(Bm, N, Kred, 64, 64, tb) : get_tmap(Bm, Kred, N, 64, pair ? bn / 2 : bn, tb);
 }
 
 void fill_tiles(UmmaParams& p, int64_t M, int64_t N, int64_t Kred, int bn, int splits) {
@@ -546,6 +809,8 @@ void fill_tiles(UmmaParams& p, int64_t M, int64_t N, int64_t Kred, int bn, int s
 
 }  // namespace
 
+void umma_set_pair(int on) { g_use_pair.store(on ? 1 : 0); }
+
 void umma_set_sm_reserve(int sms) { g_sm_reserve.store(sms < 0 ? 0 : sms); }
 
 bool umma_shape_ok(int64_t B, int64_t K, int64_t N) { return B > 0 && K >= 8 && N >= 8 && K % 8 == 0 && N % 8 == 0; }
@@ -561,6 +826,10 @@ int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64
   p.bias = bias;
   p.act = act;
   p.out = A;
+  if (pair_ok(bn, p)) {
+    if (out_dtype == DDNN_BF16) return launch_pair<false, true, EPI_FWD_BF16>(ta, tb, p, st);
+    return launch_pair<false, true, EPI_FWD_F32>(ta, tb, p, st);
+  }
   if (out_dtype == DDNN_BF16) return launch_bn<false, true, EPI_FWD_BF16>(bn, ta, tb, p, st);
   return launch_bn<false, true, EPI_FWD_F32>(bn, ta, tb, p, st);
 }
@@ -569,14 +838,16 @@ int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int6
             int act_prev, cudaStream_t st) {
   // D[B, K] = dZ[B, N] . W[K, N]^T : GEMM-N = K (layer input width), reduction = N
   const int bn = pick_bn(K);
-  CUtensorMap ta, tb;
-  int rc = operand_maps(false, dZ, false, W, B, K, N, bn, &ta, &tb);
-  if (rc != DDNN_OK) return rc;
   UmmaParams p{};
   fill_tiles(p, B, K, N, bn, 1);
   p.act = act_prev;
   p.aprev = Aprev;
   p.out = dZprev;
+  const bool pair = pair_ok(bn, p);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(false, dZ, false, W, B, K, N, bn, &ta, &tb, pair);
+  if (rc != DDNN_OK) return rc;
+  if (pair) return launch_pair<false, false, EPI_DX>(ta, tb, p, st);
   return launch_bn<false, false, EPI_DX>(bn, ta, tb, p, st);
 }
 
@@ -616,10 +887,12 @@ int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_
     p.w_master = W_master;
     p.w_shadow = W_shadow;
     p.lr = lr;
+    if (pair_ok(bn, p)) return launch_pair<true, true, EPI_SGD>(ta, tb, p, st);
     return launch_bn<true, true, EPI_SGD>(bn, ta, tb, p, st);
   }
   p.out = dW_out;
   p.zrows = 0;
+  if (pair_ok(bn, p)) return launch_pair<true, true, EPI_STORE>(ta, tb, p, st);
   return launch_bn<true, true, EPI_STORE>(bn, ta, tb, p, st);
 }
 

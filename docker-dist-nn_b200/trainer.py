@@ -190,3 +190,20 @@ class Trainer:
 
     def export_params(self) -> List[Dict[str, Any]]:
         return self.layer.export_params()
+
+    def export_config(self) -> Dict[str, Any]:
+        """The trained model in the reference's JSON schema (one neuron per output column with
+        ``weights``/``bias``/``activation``, ``type`` hidden|output, ``nodes``: the exporter layout of
+        Centralized_MNIST_Experimentation.ipynb:462-506), so the unmodified reference chain can
+        serve it; training keys and ``layer_distribution`` are carried over."""
+        from .config import params_to_layers
+        cfg = {"layers": params_to_layers(self.export_params())}
+        for k in ("layer_distribution", "learning_rate", "epochs", "batch_size", "seed", "micro_batches", "dtype"):
+            if k in self.cfg:
+                cfg[k] = self.cfg[k]
+        return cfg
+
+    def save(self, path: str) -> None:
+        import json
+        with open(path, "w") as f:
+            json.dump(self.export_config(), f)

@@ -146,6 +146,10 @@ int ddnn_dense_backward_dw_sgd_static(const void* X, const void* dZ,
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
 
+/* bf16 tcgen05 GEMMs: 1 (default) = use the CTA-pair kernel (tcgen05.mma.cta_group::2, 256x256 tile
+ * per 2-CTA cluster) when a problem has >= 2 waves of such tiles, 0 = always the single-CTA kernel. */
+int ddnn_set_cta_pairs(int on);
+
 /* fp32 path inner product for aligned forward / dW GEMMs: 0 (default) = FFMA, 1 = error-compensated
  * 3xTF32 on the tensor cores (still within the 1e-5 bound; ~4x the FFMA rounding error). */
 int ddnn_set_f32_tensor_cores(int on);

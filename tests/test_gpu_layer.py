@@ -248,3 +248,50 @@ def test_direct_output_targets_and_flags(cuda_device):
     assert flags.tolist() == [1, 1, 1, 0, 2, 2, 2, 0]
     for a, b in zip(single.export_params(), s0.export_params() + s1.export_params()):
         assert np.array_equal(a["weights"], b["weights"]) and np.array_equal(a["biases"], b["biases"])
+
+
+def layers_from_cfg(cfg):
+    from ddnn_b200.config import layers_to_params
+    return layers_to_params(cfg["layers"])
+
+
+def test_json_export_roundtrip_and_eval_driver(cuda_device, tmp_path):
+    """train on the GPU, write the model back in the reference's JSON
+    schema, reload it (bit-identical predictions), serve it through the oracle (= the reference forward)
+    and run the run_grpc_inference.py-compatible evaluation driver on an examples file."""
+    from ddnn_b200 import Trainer
+    from ddnn_b200 import infer
+    from ddnn_b200.config import load_model_config, make_config
+    dims, acts = [20, 16, 12, 4], ["relu", "sigmoid", "softmax"]
+    cfg = make_config(dims, acts, seed=6, layer_distribution=[2, 1], learning_rate=0.2, epochs=3, batch_size=32)
+    x, y = synthetic_batch(100, 20, 4, seed=2)
+    t = Trainer(cfg)
+    losses = t.fit((x, y))                       # epochs / batch size / lr from the config
+    ref = [dict(p) for p in layers_from_cfg(cfg)]
+    ref_losses = [oracle.train_step(ref, x[a:b], y[a:b], 0.2) for _ in range(3) for (a, b) in
+                  [(0, 32), (32, 64), (64, 96), (96, 100)]]
+    np.testing.assert_allclose(losses, ref_losses, rtol=F32_TOL)
+    path = tmp_path / "trained.json"
+    t.save(str(path))
+    saved = json.loads(path.read_text())
+    assert [l["nodes"] for l in saved["layers"]] == [16, 12, 4] and saved["layer_distribution"] == [2, 1]
+    assert saved["layers"][0]["type"] == "hidden" and saved["layers"][-1]["type"] == "output"
+    assert saved["layers"][1]["neurons"][0]["activation"] == "sigmoid" and len(saved["layers"][0]["neurons"][0]["weights"]) == 20
+    # reload on the GPU: identical predictions
+    t2 = Trainer(str(path))
+    assert np.array_equal(t.predict(x), t2.predict(x))
+    # the reference's forward (oracle, pinned bit-exact to grpc_node.py) on the exported file
+    ref_params = oracle.build_layer_params({f"layer_{i + 1}": l["neurons"] for i, l in enumerate(saved["layers"])})
+    ref_out = oracle.process_matrix(ref_params, x, 20)
+    assert rel_err(t.predict(x), ref_out) < F32_TOL
+    # evaluation driver: reference CLI semantics (sequential batches, ragged tail, argmax == label)
+    examples = [{"input": x[i].tolist(), "label": int(y[i])} for i in range(100)]
+    inputs = tmp_path / "examples.json"
+    inputs.write_text(json.dumps({"examples": examples}))
+    correct, n, total, per_batch = infer.evaluate(str(path), examples, batch_size=32)
+    assert n == 100 and len(per_batch) == 4
+    assert correct == int((ref_out.argmax(axis=1) == y).sum())
+    c1, n1, _, pb1 = infer.evaluate(str(path), examples, input_index=7)
+    assert n1 == 100 and len(pb1) == 1 and c1 == int(ref_out[7].argmax() == y[7])
+    assert infer.main(["--config", str(path), "--inputs", str(inputs), "--batch-size", "40"]) == 0
+    assert infer.main(["200", "--config", str(path), "--inputs", str(inputs)]) == 1  # index out of range

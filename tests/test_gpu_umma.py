@@ -132,3 +132,47 @@ def test_forward_full_size_checksum(cuda_device):
     cols = [0, 1, 255, 256, 4097, 8191]
     ref = xd.double().cpu().numpy() @ w[:, cols].double().cpu().numpy()
     assert rel_err(out[:, cols].double().cpu().numpy(), ref) < ACC_TOL
+
+
+@pytest.mark.parametrize("bkn", [(4096, 512, 4096), (4000, 320, 4104)])
+def test_cta_pair_kernels(cuda_device, bkn):
+    """Problems with >= 2 waves of 256x256 tiles run on the CTA-pair (tcgen05 cta_group::2) kernel:
+    forward, dX and dW/SGD against the oracle on the bf16-rounded operands, ragged M/N tails included,
+    and bit-identical to the single-CTA kernel (same k order)."""
+    from ddnn_b200 import _lib, ops
+    b, k, n = bkn
+    rng = np.random.default_rng(20)
+    # forward: D[b, n]
+    x = to_dev(rng.random((b, k)) - 0.25, torch.bfloat16)
+    w = to_dev(rng.standard_normal((k, n)) / np.sqrt(k), torch.bfloat16)
+    bias = to_dev(rng.standard_normal(n) * 0.1)
+    ref = oracle.activate(np.dot(to_np(x), to_np(w)) + to_np(bias), "relu")
+    got = ops.dense_forward(x, w, bias, "relu", out_dtype=torch.float32)
+    assert rel_err(to_np(got), ref) < ACC_TOL
+    # dX: D[b, k2] with k2 = n (wide input side), reduction over n2 = k
+    dz = to_dev(rng.standard_normal((b, k)) / b, torch.bfloat16)
+    w2 = to_dev(rng.standard_normal((n, k)) / np.sqrt(k), torch.bfloat16)     # layer n -> k
+    a_prev = to_dev(oracle.activate(rng.standard_normal((b, n)), "relu"), torch.bfloat16)
+    ref_dx = np.dot(to_np(dz), to_np(w2).T) * (to_np(a_prev) > 0)
+    got_dx = ops.dense_backward_dx(dz, w2, a_prev, "relu")
+    assert rel_err(to_np(got_dx), ref_dx) < BF16_OUT_TOL
+    # dW + fused SGD: D[n, n2] = X2^T dZ2 with a short reduction (rows = k)
+    x2 = to_dev(rng.random((k, n)), torch.bfloat16)
+    dz2 = to_dev(rng.standard_normal((k, n)) / k, torch.bfloat16)
+    ref_dw = np.dot(to_np(x2).T, to_np(dz2))
+    dw, db = ops.dense_backward_dw(x2, dz2)
+    assert rel_err(to_np(dw), ref_dw) < ACC_TOL and rel_err(to_np(db), to_np(dz2).sum(axis=0)) < ACC_TOL
+    wm = to_dev(rng.standard_normal((n, n)) * 0.01)
+    w0 = to_np(wm).copy()
+    bm = torch.zeros(n, device="cuda")
+    sh = torch.zeros((n, n), dtype=torch.bfloat16, device="cuda")
+    ops.dense_backward_dw_sgd(x2, dz2, wm, bm, 0.5, w_shadow=sh)
+    assert rel_err(to_np(wm), w0 - 0.5 * ref_dw) < 1e-5 and torch.equal(sh, wm.to(torch.bfloat16))
+    # single-CTA kernel on the same inputs: identical bits
+    _lib.set_cta_pairs(False)
+    try:
+        assert torch.equal(ops.dense_forward(x, w, bias, "relu", out_dtype=torch.float32), got)
+        assert torch.equal(ops.dense_backward_dx(dz, w2, a_prev, "relu"), got_dx)
+        assert torch.equal(ops.dense_backward_dw(x2, dz2)[0], dw)
+    finally:
+        _lib.set_cta_pairs(True)
