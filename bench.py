@@ -517,7 +517,13 @@ def main():
         else:
             roof = {"bound": "hbm", "achieved": dom["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
                     "frac": dom["gbs"] / peaks["hbm_gbs"]}
-        roof.update({"traffic": None, "kernel": dom["kernel"], "ms_per_launch": dom["ms"],
+        traffic = None
+        try:
+            with open(os.path.join(REPO, "profiles", "traffic.json")) as f:
+                traffic = json.load(f).get(workload, {}).get(dom["kernel"])
+        except Exception:  # noqa: BLE001
+            pass
+        roof.update({"traffic": traffic, "algorithmic_bytes": dom["bytes"], "kernel": dom["kernel"], "ms_per_launch": dom["ms"],
                      "peak_source": peaks["source"], "kernel_tflops": dom["tflops"],
                      "step_share": dom["ms"] / sum(r["ms"] for r in ks),
                      "timing": dom["how"]})
