@@ -500,6 +500,10 @@ def main():
         "model_flops_per_sample": fps,
         "tflops": value * fps / 1e12,
         "tensor_frac_of_measured_burst": value * fps / 1e12 / (world * peaks["bf16_tflops"]),
+        # activation bytes per sample x samples/s over the measured HBM peak
+        "step_hbm_bytes_per_sample": bytes_per_sample(dims, 4 if res["dtype"] == "f32" else 2),
+        "step_hbm_frac_of_measured": value * bytes_per_sample(dims, 4 if res["dtype"] == "f32" else 2) /
+                                     (world * peaks["hbm_gbs"] * 1e9),
         "peaks": peaks,
     }
     if "e2e_ms_total" in res:

@@ -1,7 +1,10 @@
 // extern "C" boundary of libddnn.so (see include/ddnn.h).  Validates arguments, picks the
 // engine (tcgen05 GEMMs for aligned bf16 layers, SIMT kernels otherwise) and launches.
 #include <cstring>
+#include <mutex>
+#include <set>
 #include <string>
+#include <utility>
 
 #include "ddnn_internal.h"
 
@@ -18,6 +21,18 @@ void set_error(const char* fmt, ...) {
   vsnprintf(buf, sizeof(buf), fmt, ap);
   va_end(ap);
   g_err = buf;
+}
+
+int ensure_dynamic_smem(const void* kernel, size_t bytes) {
+  static std::mutex mu;
+  static std::set<std::pair<const void*, int>> done;
+  int dev = 0;
+  DDNN_CUDA_CHECK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> g(mu);
+  if (done.count({kernel, dev})) return DDNN_OK;
+  DDNN_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  done.insert({kernel, dev});
+  return DDNN_OK;
 }
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }

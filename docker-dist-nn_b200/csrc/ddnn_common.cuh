@@ -40,6 +40,10 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 
 inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// Opts a kernel into `bytes` of dynamic shared memory once per (kernel, device): function attributes
+// belong to the device's context, and one process may drive several GPUs.
+int ensure_dynamic_smem(const void* kernel, size_t bytes);
+
 // ---- element access -----------------------------------------------------------------
 __device__ __forceinline__ float to_f32(float v) { return v; }
 __device__ __forceinline__ float to_f32(bf16 v) { return __bfloat162float(v); }

@@ -531,11 +531,8 @@ int launch_async(const float* A, const float* Bm, int M, int N, int K, int64_t l
                  bool veco, Epi epi, int64_t zstride, float* cs_part, int np, cudaStream_t st) {
   auto kern = simt_gemm_async_kernel<BM, BN, A_KMAJ, Epi, COLSUM>;
   constexpr size_t smem = async_smem_bytes<BM, BN, A_KMAJ>();
-  static bool attr_set = false;
-  if (!attr_set && smem > 48 * 1024) {
-    DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (smem > 48 * 1024)
+    if (int rc = ensure_dynamic_smem((const void*)kern, smem)) return rc;
   dim3 grid(cdiv(N, BN), cdiv(M, BM), splits);
   kern<<<grid, NTHREADS, smem, st>>>(A, Bm, M, N, K, lda, ldb, klen, veco, epi, zstride, cs_part, np);
   count_launch();
@@ -548,11 +545,8 @@ int launch_tf32(const float* A, const float* Bm, int M, int N, int K, int64_t ld
                 Epi epi, int64_t zstride, float* cs_part, int np, cudaStream_t st) {
   auto kern = tf32x3_gemm_kernel<BM, BN, A_KMAJ, Epi, COLSUM>;
   constexpr size_t smem = tf32_smem_bytes<BM, BN, A_KMAJ>();
-  static bool attr_set = false;
-  if (!attr_set && smem > 48 * 1024) {
-    DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  if (smem > 48 * 1024)
+    if (int rc = ensure_dynamic_smem((const void*)kern, smem)) return rc;
   dim3 grid(cdiv(N, BN), cdiv(M, BM), splits);
   kern<<<grid, NTHREADS, smem, st>>>(A, Bm, M, N, K, lda, ldb, klen, epi, zstride, cs_part, np);
   count_launch();
@@ -642,9 +636,11 @@ int simt_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev, int6
 }
 
 int simt_dw_splits(int64_t B, int64_t K, int64_t N) {
-  // enough (tile x split) CTAs for >= 2 waves of 148 SMs, at least 4 k-slabs per split
+  // fill the 2 x 148 resident CTA slots (launch bounds: 2 CTAs / SM) in ONE wave: tiles x splits <= 296
+  // (rounding up instead spilled 16 of 312 CTAs into a second wave on the MNIST layer: 2x the time),
+  // at least 4 k-slabs per split
   long tiles = (long)cdiv(K, 64) * cdiv(N, 64);
-  long want = (2 * 148 + tiles - 1) / tiles;
+  long want = (2 * 148) / tiles;
   long max_by_k = B / (4 * BK);
   if (max_by_k < 1) max_by_k = 1;
   long s = want < max_by_k ? want : max_by_k;

@@ -276,7 +276,7 @@ static int skinny_fwd_t(const void* X, const void* W, const float* bias, void* A
   do {                                                                                                        \
     auto kern = KERN;                                                                                         \
     if (smem > 48 * 1024)                                                                                     \
-      DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));    \
+      if (int rc_ = ensure_dynamic_smem((const void*)kern, smem)) return rc_;                                 \
     kern<<<(unsigned)blocks, 256, smem, st>>>((const TI*)X, (const TI*)W, bias, (TO*)A, B, (int)K, (int)N, act); \
   } while (0)
   const int nv = nv4_of(N);

@@ -66,7 +66,6 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       : "memory");
 }
 __device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
@@ -718,11 +717,7 @@ int pick_bn(int64_t n) { return n >= 192 ? 256 : (n >= 96 ? 128 : 64); }
 template <bool A_MN, bool B_MN, int BN, int EPI>
 int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p, cudaStream_t st) {
   auto kern = umma_gemm_kernel<A_MN, B_MN, BN, EPI>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg<BN>::SMEM_BYTES));
-    attr_set = true;
-  }
+  if (int rc = ensure_dynamic_smem((const void*)kern, Cfg<BN>::SMEM_BYTES)) return rc;
   const int total = p.m_blocks * p.n_blocks * p.splits;
   int ctas = num_sms() - g_sm_reserve.load();
   if (ctas < 1) ctas = 1;
@@ -738,11 +733,7 @@ std::atomic<int> g_use_pair{1};  // 1: CTA-pair (cta_group::2) kernel for large 
 template <bool A_MN, bool B_MN, int EPI>
 int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cudaStream_t st) {
   auto kern = umma_pair_gemm_kernel<A_MN, B_MN, EPI>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DDNN_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg2::SMEM_BYTES));
-    attr_set = true;
-  }
+  if (int rc = ensure_dynamic_smem((const void*)kern, Cfg2::SMEM_BYTES)) return rc;
   // tile space in 256-row blocks; rasterisation group halves accordingly
   p.m_blocks = cdiv(p.M, 256);
   p.group_m = p.group_m > 1 ? (p.group_m + 1) / 2 : 1;
