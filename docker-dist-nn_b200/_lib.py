@@ -39,6 +39,9 @@ SYMBOLS = {
     "ddnn_dw_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
     "ddnn_dense_backward_dw_sgd_static": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
                                                     _i32, _vp]),
+    "ddnn_output_layer_train": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32,
+                                          _i64, _i64, _i64, _i32, _f32, _i32, _i32, _vp, _sz, _vp]),
+    "ddnn_output_layer_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
     "ddnn_cast_f32_to_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_cast_bf16_to_f32": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_ipc_export": (C.c_int, [_vp, _vp, C.POINTER(C.c_int64)]),

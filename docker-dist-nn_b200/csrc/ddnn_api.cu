@@ -287,6 +287,58 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
   return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
 }
 
+size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
+  if (B <= 0 || K <= 0 || N <= 0) return 0;
+  (void)dtype;
+  const size_t need = (size_t)outlayer_splits(B) * ((size_t)K + 1) * np_of(N) * sizeof(float);
+  return (need + 255) & ~(size_t)255;
+}
+
+int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels, void* dZ, float* row_loss,
+                            float* loss, void* dZprev, float* W_master, void* W_shadow, float* bias, float* dW_out,
+                            float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N, int act_prev,
+                            float inv_denom, int accumulate_loss, int dtype, void* workspace,
+                            size_t workspace_bytes, void* stream) {
+  int rc = check_dims("ddnn_output_layer_train", B, K, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!A || !W || !labels || !row_loss || !bias) {
+    set_error("ddnn_output_layer_train: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (apply ? !W_master : (!dW_out || !db_out)) {
+    set_error("ddnn_output_layer_train: missing %s", apply ? "W_master" : "dW_out/db_out");
+    return DDNN_ERR_ARG;
+  }
+  if (act_prev < DDNN_ACT_LINEAR || act_prev >= DDNN_ACT_SOFTMAX) {
+    set_error("ddnn_output_layer_train: activation %d of the feeding layer is not supported", act_prev);
+    return DDNN_ERR_ACTIVATION;
+  }
+  if (!outlayer_fused_ok(A, K, N, dtype)) {
+    set_error("ddnn_output_layer_train: needs N <= 16, K <= 256, 16-byte aligned rows (got K=%lld N=%lld)",
+              (long long)K, (long long)N);
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  const size_t need = ddnn_output_layer_workspace_bytes(B, K, N, dtype);
+  if (!workspace || workspace_bytes < need || !aligned16(workspace)) {
+    set_error("ddnn_output_layer_train: workspace %zu bytes < %zu required (or misaligned)", workspace_bytes, need);
+    return DDNN_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int splits = outlayer_splits(B);
+  const size_t np = np_of(N);
+  float* dw_part = (float*)workspace;
+  float* db_part = dw_part + (size_t)splits * K * np;
+  rc = outlayer_fused(A, W, bias, labels, dZ, row_loss, dZprev, dw_part, db_part, B, K, N, act_prev, inv_denom, dtype,
+                      st);
+  if (rc) return rc;
+  if (loss) {
+    rc = loss_reduce(row_loss, loss, B, inv_denom, accumulate_loss, st);
+    if (rc) return rc;
+  }
+  return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+}
+
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream) {
   if (n <= 0) return DDNN_OK;
   if (!in || !out || !aligned16(in) || (reinterpret_cast<uintptr_t>(out) & 7u)) {

@@ -25,6 +25,14 @@ int skinny_dw_splits(int64_t B, int64_t K, int64_t N);
 int skinny_dw_partials(const void* X, const void* dZ, float* dw_part, float* db_part, int splits,
                        int64_t B, int64_t K, int64_t N, int dtype, cudaStream_t st);
 
+// ---- fused skinny output layer: logits + softmax-CE + dX + dW/db partials (ddnn_outlayer.cu) ----
+bool outlayer_fused_ok(const void* A, int64_t K, int64_t N, int dtype);
+int outlayer_splits(int64_t B);
+int outlayer_fused(const void* A, const void* W, const float* bias, const int32_t* labels, void* dZ,
+                   float* row_loss, void* dZprev, float* dw_part, float* db_part, int64_t B, int64_t K,
+                   int64_t N, int act_prev, float inv_denom, int dtype, cudaStream_t st);
+int loss_reduce(const float* row_loss, float* loss, int64_t B, float scale, int accumulate, cudaStream_t st);
+
 // ---- split-K reduction + dW epilogue (ddnn_reduce.cu) --------------------------------
 // Sums partials in z order, then SGD (apply) or fp32 store.
 int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K, int64_t N,

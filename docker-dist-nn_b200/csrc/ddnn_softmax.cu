@@ -207,6 +207,13 @@ int softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ, float*
   return DDNN_OK;
 }
 
+int loss_reduce(const float* row_loss, float* loss, int64_t B, float scale, int accumulate, cudaStream_t st) {
+  loss_reduce_kernel<<<1, 1024, 0, st>>>(row_loss, loss, B, scale, accumulate);
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+
 int activate(const float* V, float* out, int64_t B, int64_t N, int act, cudaStream_t st) {
   if (act == DDNN_ACT_SOFTMAX) return softmax_rows(V, out, B, N, st);
   activate_kernel<<<grid_for(B * N), 256, 0, st>>>(V, out, B * N, act);

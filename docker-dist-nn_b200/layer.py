@@ -213,6 +213,8 @@ class Layer:
             a.append(torch.empty((rows, n), dtype=torch.float32 if (last and self.is_output) else cdt, device=dev))
             dz.append(torch.empty((rows, n), dtype=cdt, device=dev))
         ws_bytes = max(ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp)
+        ws_bytes = max(ws_bytes, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0],
+                                                                  lp[-1]["weights"].shape[1], cdt))
         self._bufs = {
             "cap": rows, "a": a, "dz": dz,
             "dx": torch.empty((rows, lp[0]["weights"].shape[0]), dtype=cdt, device=dev),
@@ -239,7 +241,7 @@ class Layer:
         return self._bufs["a"][-1][row0:row0 + rows]
 
     def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None,
-                      out_target: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      out_target: Optional[torch.Tensor] = None, skip_last: bool = False) -> torch.Tensor:
         """Forward of rows [row0, row0+rows) keeping what backward needs.  ``x`` None means the
         rows are already in ``input_buffer``.  An output node stops at the fp32 logits Z
         (softmax is fused into ``loss_and_grad``).  ``out_target`` (rows, N_last) redirects the
@@ -260,6 +262,8 @@ class Layer:
         n_layers = len(self.layer_params)
         for i, p in enumerate(self.layer_params):
             last = i == n_layers - 1
+            if last and skip_last:  # the fused output-layer step computes the logits itself
+                break
             act = p["activation"]
             if last and self.is_output:
                 if act in ("relu", "sigmoid"):
@@ -320,20 +324,22 @@ class Layer:
                 ops.dense_backward_dw_sgd(b["a"][i][:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
                                           w_shadow=self._shadow[i], workspace=self._ws)
 
-    def backward_and_step(self, lr: float, rows: Optional[int] = None, side: Optional[torch.cuda.Stream] = None) -> None:
+    def backward_and_step(self, lr: float, rows: Optional[int] = None, side: Optional[torch.cuda.Stream] = None,
+                          top: Optional[int] = None) -> None:
         """backward() + step() for a single-node model with the weight updates of the upper layers
         running on ``side`` beside the dX chain: dW_l starts as soon as dX_l (the last reader of the
         old W_l) has finished, so only  dX_L .. dX_2 -> dW_1  stays on the critical path.  Works
         eagerly and under CUDA-graph capture (the cross-stream events become graph edges)."""
         rows = self._rows if rows is None else rows
-        if side is None or len(self.layer_params) < 2:
-            self.backward(0, rows, need_input_grad=False)
-            self.step(lr, rows)
+        top = len(self.layer_params) - 1 if top is None else top  # highest layer still to be processed
+        if top < 0:
             return
+        if side is None:
+            side = torch.cuda.current_stream(self.device)
         b = self._bufs
         main = torch.cuda.current_stream(self.device)
         sl = slice(0, rows)
-        for i in range(len(self.layer_params) - 1, 0, -1):
+        for i in range(top, 0, -1):
             p = self.layer_params[i]
             k_, n_ = p["weights"].shape
             with self._span(f"dX L{i + 1} {n_}->{k_}"):
@@ -351,6 +357,43 @@ class Layer:
             ops.dense_backward_dw_sgd(b["a"][0][sl], b["dz"][0][sl], p["weights"], p["biases"], lr,
                                       w_shadow=self._shadow[0], workspace=self._ws)
         main.wait_stream(side)
+
+    def can_fuse_output_layer(self) -> bool:
+        """True when the last local layer is the network's skinny output layer (N <= 16, K <= 256,
+        softmax / linear) that ``output_layer_step`` can run as one kernel."""
+        if not self.is_output or self._bufs is None:
+            return False
+        p = self.layer_params[-1]
+        if p["activation"] in ("relu", "sigmoid"):
+            return False
+        prev_act = self.layer_params[-2]["activation"] if len(self.layer_params) > 1 else self.input_activation
+        if prev_act == "softmax":
+            return False
+        k, n = p["weights"].shape
+        return ops.output_layer_supported(self._bufs["a"][-2], k, n)
+
+    def output_layer_step(self, labels: torch.Tensor, lr: float, rows: Optional[int] = None,
+                          denom: Optional[int] = None, need_input_grad: bool = True) -> torch.Tensor:
+        """Forward + softmax-CE + dX + dW/db + SGD of the output layer in one pass over its input
+        (``ddnn_output_layer_train``).  Call after ``forward_train(..., skip_last=True)``; fills dZ of the
+        layer below (already multiplied by that layer's activation derivative) and the device loss."""
+        rows = self._rows if rows is None else rows
+        b = self._bufs
+        i = len(self.layer_params) - 1
+        p = self.layer_params[i]
+        prev_act = self.layer_params[i - 1]["activation"] if i > 0 else self.input_activation
+        dz_prev = None
+        if i > 0:
+            dz_prev = b["dz"][i - 1][:rows]
+        elif need_input_grad:
+            dz_prev = b["dx"][:rows]
+        k_, n_ = p["weights"].shape
+        with self._span(f"output layer fused {k_}->{n_}"):
+            ops.output_layer_train(b["a"][i][:rows], self._w(i), labels, b["row_loss"][:rows], b["loss"],
+                                   1.0 / float(rows if denom is None else denom), prev_act, self._ws,
+                                   w_master=p["weights"], bias=p["biases"], lr=lr, w_shadow=self._shadow[i],
+                                   dz=b["dz"][i][:rows], dz_prev=dz_prev)
+        return b["loss"]
 
     def gradients(self, rows: Optional[int] = None):
         """[(dW, db)] per local layer from the buffered activations/gradients (no update)."""

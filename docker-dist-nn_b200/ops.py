@@ -142,6 +142,37 @@ def dense_backward_dw_sgd(x: torch.Tensor, dz: torch.Tensor, w_master: torch.Ten
                                              1, b, k, n, _DT[x.dtype], _p(ws), ws.numel(), _stream(x)))
 
 
+def output_layer_supported(a: torch.Tensor, k: int, n: int) -> bool:
+    """Shapes the fused output-layer step handles (ddnn_output_layer_train): N <= 16, K <= 256, rows of
+    the input 16-byte aligned and at most 64 16-byte chunks long."""
+    e = 4 if a.dtype == torch.float32 else 8
+    return 1 <= n <= 16 and 1 <= k <= 256 and k % e == 0 and a.data_ptr() % 16 == 0
+
+
+def output_layer_workspace_bytes(b: int, k: int, n: int, dtype: torch.dtype) -> int:
+    return int(lib.ddnn_output_layer_workspace_bytes(b, k, n, _DT[dtype]))
+
+
+def output_layer_train(a: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, row_loss: torch.Tensor,
+                       loss: Optional[torch.Tensor], inv_denom: float, act_prev, workspace: torch.Tensor,
+                       w_master: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, lr: float = 0.0,
+                       w_shadow: Optional[torch.Tensor] = None, dz: Optional[torch.Tensor] = None,
+                       dz_prev: Optional[torch.Tensor] = None, dw_out: Optional[torch.Tensor] = None,
+                       db_out: Optional[torch.Tensor] = None, accumulate_loss: bool = False) -> None:
+    """Fused skinny output layer: logits + softmax-CE + dX + dW/db (+ SGD when ``w_master`` is given)."""
+    _req(a, name="a"); _req(w, a.dtype, "w"); _req(labels, torch.int32, "labels")
+    _req(row_loss, torch.float32, "row_loss"); _req(bias, torch.float32, "bias")
+    b, k = a.shape
+    n = w.shape[1]
+    apply = 1 if w_master is not None else 0
+    act_id = act_prev if isinstance(act_prev, int) else _lib.activation_id(act_prev)
+    with torch.cuda.device(a.device):
+        check(lib.ddnn_output_layer_train(_p(a), _p(w), _p(labels), _p(dz), _p(row_loss), _p(loss), _p(dz_prev),
+                                          _p(w_master), _p(w_shadow), _p(bias), _p(dw_out), _p(db_out), float(lr),
+                                          apply, b, k, n, act_id, float(inv_denom), 1 if accumulate_loss else 0,
+                                          _DT[a.dtype], _p(workspace), workspace.numel(), _stream(a)))
+
+
 def _workspace(ws: Optional[torch.Tensor], b: int, k: int, n: int, like: torch.Tensor) -> torch.Tensor:
     need = dw_workspace_bytes(b, k, n, like.dtype)
     if ws is None or ws.numel() < need:

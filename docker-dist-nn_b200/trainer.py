@@ -47,9 +47,16 @@ class Trainer:
         device loss scalar (mean CE before the update); does not synchronise."""
         L = self.layer
         L.begin_batch(x.shape[0])
+        lr = self.lr if lr is None else lr
+        if L.can_fuse_output_layer():
+            # skinny output layer: logits, softmax-CE, dX, dW/db and the SGD update in one pass over its input
+            L.forward_train(x, 0, skip_last=True)
+            loss = L.output_layer_step(labels, lr, x.shape[0], need_input_grad=False)
+            L.backward_and_step(lr, x.shape[0], side=self._side, top=len(L.layer_params) - 2)
+            return loss
         L.forward_train(x, 0)
         loss = L.loss_and_grad(labels, 0)
-        L.backward_and_step(self.lr if lr is None else lr, x.shape[0], side=self._side)
+        L.backward_and_step(lr, x.shape[0], side=self._side)
         return loss
 
     def capture(self, rows: int, lr: Optional[float] = None, x_dtype: torch.dtype = torch.float32) -> None:

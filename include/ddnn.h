@@ -142,6 +142,23 @@ int ddnn_dense_backward_dw_sgd_static(const void* X, const void* dZ,
                                       float lr, int apply,
                                       int64_t B, int64_t K, int64_t N, int dtype, void* stream);
 
+/*
+ * Whole training step of a skinny OUTPUT layer in one pass over its input A[B,K] (N <= 16 classes,
+ * K <= 256, rows of A 16-byte aligned; otherwise DDNN_ERR_UNSUPPORTED -- use the separate entry points):
+ *   logits = A.W + bias ; softmax-CE (row_loss, *loss, dZ = (p - onehot) * inv_denom)
+ *   dZprev = (dZ.W^T) * f'(A)  with f' of the FEEDING layer's activation (nullable: no input gradient)
+ *   dW = A^T.dZ, db = sum dZ   then SGD (apply) or fp32 store, like ddnn_dense_backward_dw_sgd
+ * W is the operand the GEMMs read (bf16 shadow in bf16 mode, the fp32 weight in f32 mode); W_master/W_shadow
+ * /bias are what the update writes.  dZ is optional.  No reference counterpart (grpc_node.py has no loss).
+ */
+int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels, void* dZ,
+                            float* row_loss, float* loss, void* dZprev,
+                            float* W_master, void* W_shadow, float* bias, float* dW_out, float* db_out,
+                            float lr, int apply, int64_t B, int64_t K, int64_t N, int act_prev,
+                            float inv_denom, int accumulate_loss, int dtype,
+                            void* workspace, size_t workspace_bytes, void* stream);
+size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype);
+
 /* out[i] = bf16(in[i]) / fp32(in[i]) converters for staging host-provided fp32 data. */
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);

@@ -231,3 +231,54 @@ def test_f32_inner_product_cores(cuda_device, shape, tensor_cores):
         assert rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
     finally:
         _lib.set_f32_tensor_cores(False)
+
+
+@pytest.mark.parametrize("case", [(4096, 64, 10, "f32", "relu"), (1000, 16, 3, "f32", "sigmoid"),
+                                  (300, 256, 16, "f32", "linear"), (777, 128, 1, "f32", "relu"),
+                                  (65536, 256, 10, "bf16", "relu"), (513, 64, 13, "bf16", "sigmoid")])
+def test_fused_output_layer_step(cuda_device, case):
+    """ddnn_output_layer_train: logits + softmax-CE + dX + dW/db (+ SGD) of a skinny output layer in one
+    pass, against the oracle evaluated on the operands as the kernel sees them."""
+    from ddnn_b200 import ops
+    b, k, n, dt, act_prev = case
+    tdt = torch.float32 if dt == "f32" else torch.bfloat16
+    rng = np.random.default_rng(30)
+    a = oracle.activate(rng.standard_normal((b, k)), act_prev)
+    w = rng.standard_normal((k, n)) / np.sqrt(k)
+    bias = rng.standard_normal(n) * 0.1
+    y = rng.integers(0, n, size=b)
+    ad, wd = to_dev(a, tdt), to_dev(w, tdt)
+    ar, wr = to_np(ad), to_np(wd)
+    assert ops.output_layer_supported(ad, k, n)
+    loss, _, dz = oracle.softmax_ce(ar @ wr + bias, y)
+    zprev_sign = {"relu": (ar > 0).astype(np.float64), "sigmoid": ar * (1 - ar), "linear": np.ones_like(ar)}[act_prev]
+    ref_dx = (dz @ wr.T) * zprev_sign
+    ws = torch.empty(max(256, ops.output_layer_workspace_bytes(b, k, n, tdt)), dtype=torch.uint8, device="cuda")
+    row_loss = torch.empty(b, device="cuda")
+    ls = torch.zeros(1, device="cuda")
+    dzd = torch.empty((b, n), dtype=tdt, device="cuda")
+    dxd = torch.empty((b, k), dtype=tdt, device="cuda")
+    dw = torch.empty((k, n), device="cuda")
+    db = torch.empty(n, device="cuda")
+    bd = to_dev(bias)
+    ops.output_layer_train(ad, wd, to_dev(y, torch.int32), row_loss, ls, 1.0 / b, act_prev, ws, bias=bd, dz=dzd,
+                           dz_prev=dxd, dw_out=dw, db_out=db)
+    out_tol = F32_TOL if dt == "f32" else 6e-3   # bf16 outputs carry one rounding
+    assert abs(ls.item() - loss) < F32_TOL * abs(loss) + 1e-7
+    assert rel_err(to_np(dzd), dz) < out_tol
+    assert rel_err(to_np(dxd), ref_dx) < out_tol
+    assert rel_err(to_np(dw), ar.T @ dz) < F32_TOL
+    assert rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+    # fused SGD update, twice (the second call finds the first call's partials in the workspace)
+    wm = to_dev(wr)
+    sh = to_dev(wr, torch.bfloat16) if dt == "bf16" else None
+    for step in range(2):
+        w_before, b_before = to_np(wm).copy(), to_np(bd).copy()
+        w_used = to_np(sh) if dt == "bf16" else w_before
+        _, _, dz2 = oracle.softmax_ce(ar @ w_used + b_before, y)
+        ops.output_layer_train(ad, sh if dt == "bf16" else wm, to_dev(y, torch.int32), row_loss, ls, 1.0 / b, act_prev,
+                               ws, w_master=wm, bias=bd, lr=0.3, w_shadow=sh)
+        assert rel_err(to_np(wm), w_before - 0.3 * (ar.T @ dz2)) < F32_TOL
+        assert rel_err(to_np(bd), b_before - 0.3 * dz2.sum(axis=0)) < F32_TOL
+        if sh is not None:
+            assert torch.equal(sh, wm.to(torch.bfloat16))
