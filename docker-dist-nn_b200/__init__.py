@@ -21,7 +21,7 @@ def __getattr__(name):  # lazy: keep `import ddnn_b200.config` free of torch/CUD
     if name == "PipelineStage":
         from .pipeline import PipelineStage
         return PipelineStage
-    if name in ("ops", "_lib", "layer", "trainer", "pipeline", "build"):
+    if name in ("ops", "_lib", "layer", "trainer", "pipeline", "build", "infer", "grpc_shim"):
         import importlib
         return importlib.import_module(f"{__name__}.{name}")
     raise AttributeError(name)
