@@ -271,12 +271,8 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
     if (rc) return rc;
     rc = colsum_partials(dZ, db_part, cs, B, N, dtype, st);
     if (rc) return rc;
-    if (splits > 1 && cs != splits) {
-      // two reductions with different split counts: weights first, then the bias row
-      rc = reduce_dw(dw_part, nullptr, splits, K, N, W_master, W_shadow, nullptr, dW_out, nullptr, lr, apply, st);
-      if (rc) return rc;
-      return reduce_dw(nullptr, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
-    }
+    if (splits > 1)  // weights (splits) and bias row (cs) reduced in one launch
+      return reduce_dw2(dw_part, db_part, splits, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
     return reduce_dw(dw_part, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
   }
   const int splits = simt_dw_splits(B, K, N);

@@ -38,6 +38,10 @@ int loss_reduce(const float* row_loss, float* loss, int64_t B, float scale, int 
 int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K, int64_t N,
               float* W_master, void* W_shadow, float* bias, float* dW_out, float* db_out, float lr,
               int apply, cudaStream_t st);
+// same with separate split counts for the dW partials and the db partials (one launch instead of two)
+int reduce_dw2(const float* dw_part, const float* db_part, int splits, int splits_b, int64_t K, int64_t N,
+               float* W_master, void* W_shadow, float* bias, float* dW_out, float* db_out, float lr,
+               int apply, cudaStream_t st);
 // db partials from dZ alone (used by the tcgen05 path): db_part[z][Np]
 int colsum_partials(const void* dZ, float* db_part, int splits, int64_t B, int64_t N, int dtype,
                     cudaStream_t st);

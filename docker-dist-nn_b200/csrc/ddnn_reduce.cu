@@ -11,7 +11,8 @@ namespace {
 // only on (splits, G), so the result is run-to-run deterministic.
 template <int G, typename EpiW, typename EpiB>
 __global__ void __launch_bounds__(256)
-reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part, int splits, int64_t rows,
+reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part, int splits_w, int splits_b,
+                 int64_t rows,
                  int np, int N, EpiW ew, EpiB eb, bool vecw, bool vecb, int has_db) {
   const int q = np >> 2;
   const int64_t total = (rows + (has_db ? 1 : 0)) * q;
@@ -27,6 +28,7 @@ reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db
     const bool is_w = row < rows;
     const float* base = is_w ? dw_part + row * np + col : db_part + col;
     const int64_t zs = is_w ? rows * np : np;
+    const int splits = is_w ? splits_w : splits_b;  // the bias row may come from a different split plan
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (active) {
       int z = sub;
@@ -153,18 +155,25 @@ bool vec_ok(const T* p, int64_t ld) {
 
 int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K, int64_t N, float* W_master,
               void* W_shadow, float* bias, float* dW_out, float* db_out, float lr, int apply, cudaStream_t st) {
+  return reduce_dw2(dw_part, db_part, splits, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+}
+
+int reduce_dw2(const float* dw_part, const float* db_part, int splits, int splits_b, int64_t K, int64_t N,
+               float* W_master,
+              void* W_shadow, float* bias, float* dW_out, float* db_out, float lr, int apply, cudaStream_t st) {
   const int np = (int)((N + 3) & ~(int64_t)3);
   const int64_t rows = dw_part ? K : 0;  // no dW partials: only the bias row is reduced
   const int has_db = db_part != nullptr;
   const int64_t total = (rows + has_db) * (np / 4);
   if (total == 0) return DDNN_OK;
-  const int G = splits <= 8 ? 1 : (splits <= 64 ? 8 : 32);
+  const int smax = splits > splits_b ? splits : splits_b;
+  const int G = smax <= 8 ? 1 : (smax <= 64 ? 8 : 32);
   // grid: whole groups per block; the grid-stride loop needs gridDim*256 to be a multiple of G (it is)
   long blocks = (long)((total * G + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
 #define DDNN_REDUCE(GG, EW, EB, ew, eb, vw, vb)                                                              \
-  reduce_dw_kernel<GG, EW, EB><<<(unsigned)blocks, 256, 0, st>>>(dw_part, db_part, splits, rows, np, (int)N, ew, \
+  reduce_dw_kernel<GG, EW, EB><<<(unsigned)blocks, 256, 0, st>>>(dw_part, db_part, splits, splits_b, rows, np, (int)N, ew, \
                                                               eb, vw, vb, has_db)
   if (apply) {
     EpiSgd ew{W_master, (bf16*)W_shadow, N, lr};
