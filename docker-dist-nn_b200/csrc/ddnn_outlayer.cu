@@ -157,7 +157,8 @@ outlayer_fused_kernel(const T* __restrict__ A, const T* __restrict__ W, const fl
       for (int r = 0; r < TILE_ROWS; ++r) dbs += dzs[r][threadIdx.x];
     }
     if (k < K) {
-#pragma unroll
+#pragma unroll 1  // keep the body (16 rows x N FMAs) resident in the instruction cache: fully unrolled, ncu showed
+                  // "no instruction" as a top stall and 2x the instruction count
       for (int rg = 0; rg < TILE_ROWS; rg += 16) {
         float a16[16];
 #pragma unroll
