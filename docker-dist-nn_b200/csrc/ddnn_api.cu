@@ -86,6 +86,7 @@ int ddnn_set_engine(int engine) {
     return DDNN_ERR_ARG;
   }
   g_engine.store(engine);
+  outlayer_set_tensor_cores(engine != DDNN_ENGINE_SIMT);  // SIMT pins the fused output layer to its FFMA variant
   return DDNN_OK;
 }
 
@@ -285,8 +286,8 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
 
 size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
   if (B <= 0 || K <= 0 || N <= 0) return 0;
-  (void)dtype;
-  const size_t need = (size_t)outlayer_splits(B) * ((size_t)K + 1) * np_of(N) * sizeof(float);
+  if (!outlayer_fused_ok(nullptr, K, N, dtype)) return 0;  // shapes the entry point rejects need no scratch
+  const size_t need = (size_t)outlayer_max_splits(B, K, dtype) * ((size_t)K + 1) * np_of(N) * sizeof(float);
   return (need + 255) & ~(size_t)255;
 }
 
@@ -321,7 +322,7 @@ int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels,
     return DDNN_ERR_WORKSPACE;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  const int splits = outlayer_splits(B);
+  const int splits = outlayer_splits(B, K, dtype);
   const size_t np = np_of(N);
   float* dw_part = (float*)workspace;
   float* db_part = dw_part + (size_t)splits * K * np;

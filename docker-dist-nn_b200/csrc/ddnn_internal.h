@@ -27,7 +27,9 @@ int skinny_dw_partials(const void* X, const void* dZ, float* dw_part, float* db_
 
 // ---- fused skinny output layer: logits + softmax-CE + dX + dW/db partials (ddnn_outlayer.cu) ----
 bool outlayer_fused_ok(const void* A, int64_t K, int64_t N, int dtype);
-int outlayer_splits(int64_t B);
+int outlayer_splits(int64_t B, int64_t K, int dtype);      // of the variant the current engine setting selects
+int outlayer_max_splits(int64_t B, int64_t K, int dtype);  // over both variants (workspace sizing)
+void outlayer_set_tensor_cores(int on);  // bf16: 1 = mma.sync variant (default), 0 = FFMA variant
 int outlayer_fused(const void* A, const void* W, const float* bias, const int32_t* labels, void* dZ,
                    float* row_loss, void* dZprev, float* dw_part, float* db_part, int64_t B, int64_t K,
                    int64_t N, int act_prev, float inv_denom, int dtype, cudaStream_t st);

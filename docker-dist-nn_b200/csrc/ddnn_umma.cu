@@ -170,13 +170,15 @@ __device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
       "h"((uint16_t)3)
       : "memory");
 }
-// arrive on the barrier at the same offset in CTA `rank` of the cluster
+// arrive on the barrier at the same offset in CTA `rank` of the cluster.  Default semantics (release at CTA
+// scope, like a local arrive): the accumulator hand-over is ordered by tcgen05.fence::before_thread_sync, and
+// a cluster-scope release would make the lane wait for all of its outstanding global stores (MEMBAR) per tile.
 __device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
   asm volatile(
       "{\n"
       ".reg .b32 ra;\n"
       "mapa.shared::cluster.u32 ra, %0, %1;\n"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n"
       "}\n" ::"r"(bar),
       "r"(rank)
       : "memory");
@@ -245,99 +247,121 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, const UmmaParams& p) 
 
 // Epilogue of one 128 x BN accumulator tile for the warp owning TMEM lanes [32q, 32q+32).
 // row0 = first output row of this warp, n0 = first output column of the tile.
+//
+// Each thread holds one accumulator ROW (TMEM lane) x 32 columns.  A 32x32 transpose through
+// shared memory regroups that as lane = (row r8 = lane/4, 8 consecutive columns cg = lane%4): one
+// warp instruction then touches 8 rows x 64 B (bf16) / 128 B (fp32) contiguous per row and every
+// global access is a 16-byte vector.  The chain per 32-column chunk (tcgen05.ld -> transpose ->
+// operand loads -> math -> store) is latency-bound for short reductions (K <= 1024: ncu showed the
+// epilogue warps never waiting for an accumulator), so it is software-pipelined: the TMEM load of chunk
+// c+1 is in flight while chunk c is processed, and the global operand loads of a chunk (bias / A_prev /
+// W_master) are issued before its transpose.
 template <int BN, int EPI>
-__device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, uint32_t tmem_acc, int row0, int n0,
-                                              int64_t zoff, int q, int lane) {
-  // Each thread holds one accumulator ROW (TMEM lane) x 32 columns.  A 32x32 transpose through
-  // shared memory regroups that as lane = (row r8 = lane/4, 8 consecutive columns cg = lane%4): one
-  // warp instruction then touches 8 rows x 64 B (bf16) / 128 B (fp32) contiguous per row, every
-  // global access is a 16-byte vector, and a lane issues its 4 row-loads (A_prev / W) together.
-  const int nrows = min(32, p.M - row0);  // warp-uniform
+__device__ __forceinline__ void epilogue_chunk(const UmmaParams& p, float* stg, const float (&v)[32], int nrows,
+                                               int64_t idx0, int col, int lane) {
   const int cg = lane & 3, r8 = lane >> 2;
-#pragma unroll 1
-  for (int c = 0; c < BN / 32; ++c) {
-    float v[32];
-    tmem_ld32(tmem_acc + c * 32 + ((uint32_t)(q * 32) << 16), v);
-    tmem_ld_wait();
+  const bool in = col < p.N;  // N % 8 == 0: a group of 8 columns is all in or all out
+  float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+  uint4 ap[4];          // EPI_DX: 8 bf16 of A_prev per row
+  float4 w0[4], w1[4];  // EPI_SGD: 8 fp32 of W_master per row
+  if (in) {
+    if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+      b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+      b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
+    }
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      *reinterpret_cast<float4*>(&stg[lane * Cfg<BN>::STG_PITCH + 4 * j]) =
-          make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-    __syncwarp();
-    const int col = n0 + c * 32 + cg * 8;  // N % 8 == 0: a group of 8 columns is all in or all out
-    if (col < p.N) {
-      const int64_t idx0 = ((int64_t)row0 + zoff) * p.N + col;
-      float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+    for (int it = 0; it < 4; ++it) {
+      const int r = it * 8 + r8;
+      if (EPI == EPI_DX) {
+        ap[it] = make_uint4(0, 0, 0, 0);
+        if (p.act != DDNN_ACT_LINEAR && r < nrows)
+          ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
+      }
+      if (EPI == EPI_SGD) {
+        w0[it] = w1[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < nrows) {
+          w0[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N);
+          w1[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N + 4);
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    *reinterpret_cast<float4*>(&stg[lane * Cfg<BN>::STG_PITCH + 4 * j]) =
+        make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  __syncwarp();
+  if (in) {
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int r = it * 8 + r8;
+      if (r >= nrows) continue;
+      const float4 x0 = *reinterpret_cast<const float4*>(&stg[r * Cfg<BN>::STG_PITCH + cg * 8]);
+      const float4 x1 = *reinterpret_cast<const float4*>(&stg[r * Cfg<BN>::STG_PITCH + cg * 8 + 4]);
+      float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+      const int64_t idx = idx0 + (int64_t)r * p.N;
       if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
-        b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-        b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-      }
-      uint4 ap[4];         // EPI_DX: 8 bf16 of A_prev per row
-      float4 w0[4], w1[4];  // EPI_SGD: 8 fp32 of W_master per row
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int r = it * 8 + r8;
-        if (EPI == EPI_DX) {
-          ap[it] = make_uint4(0, 0, 0, 0);
-          if (p.act != DDNN_ACT_LINEAR && r < nrows)
-            ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
-        }
-        if (EPI == EPI_SGD) {
-          w0[it] = w1[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (r < nrows) {
-            w0[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N);
-            w1[it] = *reinterpret_cast<const float4*>(p.w_master + idx0 + (int64_t)r * p.N + 4);
+        for (int e = 0; e < 8; ++e) x[e] = act_fwd(x[e] + bb[e], p.act);
+      } else if (EPI == EPI_DX) {
+        if (p.act != DDNN_ACT_LINEAR) {
+          const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&ap[it]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 a = __bfloat1622float2(a2[e]);
+            x[2 * e] *= act_bwd(a.x, p.act);
+            x[2 * e + 1] *= act_bwd(a.y, p.act);
           }
         }
+      } else if (EPI == EPI_SGD) {
+        const float ww[8] = {w0[it].x, w0[it].y, w0[it].z, w0[it].w, w1[it].x, w1[it].y, w1[it].z, w1[it].w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) x[e] = ww[e] - p.lr * x[e];
       }
+      if (EPI == EPI_FWD_BF16 || EPI == EPI_DX) {
+        uint4 o;
+        __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int r = it * 8 + r8;
-        if (r >= nrows) continue;
-        const float4 x0 = *reinterpret_cast<const float4*>(&stg[r * Cfg<BN>::STG_PITCH + cg * 8]);
-        const float4 x1 = *reinterpret_cast<const float4*>(&stg[r * Cfg<BN>::STG_PITCH + cg * 8 + 4]);
-        float x[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-        const int64_t idx = idx0 + (int64_t)r * p.N;
-        if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-          for (int e = 0; e < 8; ++e) x[e] = act_fwd(x[e] + bb[e], p.act);
-        } else if (EPI == EPI_DX) {
-          if (p.act != DDNN_ACT_LINEAR) {
-            const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&ap[it]);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const float2 a = __bfloat1622float2(a2[e]);
-              x[2 * e] *= act_bwd(a.x, p.act);
-              x[2 * e + 1] *= act_bwd(a.y, p.act);
-            }
-          }
-        } else if (EPI == EPI_SGD) {
-          const float ww[8] = {w0[it].x, w0[it].y, w0[it].z, w0[it].w, w1[it].x, w1[it].y, w1[it].z, w1[it].w};
-#pragma unroll
-          for (int e = 0; e < 8; ++e) x[e] = ww[e] - p.lr * x[e];
-        }
-        if (EPI == EPI_FWD_BF16 || EPI == EPI_DX) {
+        for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+        *reinterpret_cast<uint4*>((bf16*)p.out + idx) = o;
+      } else {
+        float* dst = EPI == EPI_SGD ? p.w_master + idx : (float*)p.out + idx;
+        *reinterpret_cast<float4*>(dst) = make_float4(x[0], x[1], x[2], x[3]);
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(x[4], x[5], x[6], x[7]);
+        if (EPI == EPI_SGD && p.w_shadow) {
           uint4 o;
           __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
 #pragma unroll
           for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
-          *reinterpret_cast<uint4*>((bf16*)p.out + idx) = o;
-        } else {
-          float* dst = EPI == EPI_SGD ? p.w_master + idx : (float*)p.out + idx;
-          *reinterpret_cast<float4*>(dst) = make_float4(x[0], x[1], x[2], x[3]);
-          *reinterpret_cast<float4*>(dst + 4) = make_float4(x[4], x[5], x[6], x[7]);
-          if (EPI == EPI_SGD && p.w_shadow) {
-            uint4 o;
-            __nv_bfloat162* o2 = reinterpret_cast<__nv_bfloat162*>(&o);
-#pragma unroll
-            for (int e = 0; e < 4; ++e) o2[e] = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
-            *reinterpret_cast<uint4*>(p.w_shadow + idx) = o;
-          }
+          *reinterpret_cast<uint4*>(p.w_shadow + idx) = o;
         }
       }
     }
-    __syncwarp();
+  }
+  __syncwarp();
+}
+
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, uint32_t tmem_acc, int row0, int n0,
+                                              int64_t zoff, int q, int lane) {
+  static_assert((BN / 32) % 2 == 0, "chunks are processed in pairs");
+  const int nrows = min(32, p.M - row0);  // warp-uniform
+  const int cg = lane & 3;
+  const uint32_t tbase = tmem_acc + ((uint32_t)(q * 32) << 16);
+  const int64_t rbase = ((int64_t)row0 + zoff) * p.N;
+  float va[32], vb[32];
+  tmem_ld32(tbase, va);
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; c += 2) {
+    tmem_ld_wait();                        // chunk c has landed in va
+    tmem_ld32(tbase + (c + 1) * 32, vb);   // chunk c+1 streams in while chunk c is processed
+    int col = n0 + c * 32 + cg * 8;
+    epilogue_chunk<BN, EPI>(p, stg, va, nrows, rbase + col, col, lane);
+    tmem_ld_wait();
+    if (c + 2 < BN / 32) tmem_ld32(tbase + (c + 2) * 32, va);
+    col += 32;
+    epilogue_chunk<BN, EPI>(p, stg, vb, nrows, rbase + col, col, lane);
   }
 }
 

@@ -34,6 +34,11 @@ def test_host_only_entry_points():
         assert _lib.activation_id(other) == _lib.ACT_LINEAR
     assert _lib.lib.ddnn_dw_workspace_bytes(4096, 784, 128, _lib.F32) > 0
     assert _lib.lib.ddnn_dw_workspace_bytes(0, 784, 128, _lib.F32) == 0
+    # the fused output layer only needs scratch for shapes it accepts (N <= 16, K <= 256); a wide layer must
+    # not size the caller's workspace (regression: 512 GiB asked for a 16384 x 16384 layer)
+    assert 0 < _lib.lib.ddnn_output_layer_workspace_bytes(65536, 256, 10, _lib.BF16) < 16 << 20
+    assert _lib.lib.ddnn_output_layer_workspace_bytes(65536, 16384, 16384, _lib.BF16) == 0
+    assert _lib.lib.ddnn_output_layer_workspace_bytes(2048, 8192, 8192, _lib.BF16) == 0
     # argument errors are reported through the status code + ddnn_last_error, never thrown
     rc = _lib.lib.ddnn_dense_forward(None, None, None, None, 4, 0, 3, 0, 0, 0, None)
     assert rc == _lib.ERR_DIM and "bad dimensions" in _lib.last_error()

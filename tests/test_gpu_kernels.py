@@ -235,10 +235,13 @@ def test_f32_inner_product_cores(cuda_device, shape, tensor_cores):
 
 @pytest.mark.parametrize("case", [(4096, 64, 10, "f32", "relu"), (1000, 16, 3, "f32", "sigmoid"),
                                   (300, 256, 16, "f32", "linear"), (777, 128, 1, "f32", "relu"),
-                                  (65536, 256, 10, "bf16", "relu"), (513, 64, 13, "bf16", "sigmoid")])
+                                  (65536, 256, 10, "bf16", "relu"), (513, 64, 13, "bf16", "sigmoid"),
+                                  (1000, 48, 16, "bf16", "linear"), (130, 256, 2, "bf16", "relu"),
+                                  (20000, 128, 9, "bf16", "sigmoid"), (513, 24, 5, "bf16", "relu")])
 def test_fused_output_layer_step(cuda_device, case):
     """ddnn_output_layer_train: logits + softmax-CE + dX + dW/db (+ SGD) of a skinny output layer in one
-    pass, against the oracle evaluated on the operands as the kernel sees them."""
+    pass, against the oracle evaluated on the operands as the kernel sees them.  bf16 with K % 16 == 0 runs the
+    mma.sync variant (128-row tiles, ragged last tile, K < 256 leaves warps without features), K = 24 the FFMA one."""
     from ddnn_b200 import ops
     b, k, n, dt, act_prev = case
     tdt = torch.float32 if dt == "f32" else torch.bfloat16
