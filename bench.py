@@ -300,7 +300,10 @@ def _kernel_work(L, rows, dtype):
         work[f"dX L{i + 1} {n}->{k}"] = (fl, rows * n * elt + k * n * elt + 2 * rows * k * elt)
         work[f"dW+SGD L{i + 1} {k}x{n}"] = (fl, rows * k * elt + rows * n * elt + 2 * k * n * 4 +
                                             (k * n * 2 if dtype == "bf16" else 0))
-    n_out = L.layer_params[-1]["weights"].shape[1]
+    k_out, n_out = L.layer_params[-1]["weights"].shape
+    # fused skinny output layer: one read of its input, one write of the gradient below it, labels, row losses, dZ
+    work[f"output layer fused {k_out}->{n_out}"] = (6.0 * rows * k_out * n_out,
+                                                    2 * rows * k_out * elt + rows * 8 + rows * n_out * elt)
     work[f"softmax-CE N={n_out}"] = (5.0 * rows * n_out, rows * n_out * (4 + elt) + rows * 8)
     return work
 
@@ -339,8 +342,13 @@ def kernel_roofline(tr, xs, ys, dtype, steps, device, use_graph):
         calls = []
         n_layers = len(L.layer_params)
         xin = xs if xs[0].dtype == L.wire_dtype else None  # layer-1 operands straight from the batch pool
+        fused_out = L.can_fuse_output_layer()
         for i, p in enumerate(L.layer_params):
             k, n = p["weights"].shape
+            if fused_out and i == n_layers - 1:  # what train_step launches for this layer: one fused entry point
+                calls.append((f"output layer fused {k}->{n}", False,
+                              lambda j: L.output_layer_step(ys[j % len(ys)], 0.0, rows)))
+                continue
             act = "linear" if i == n_layers - 1 else p["activation"]
             src = (lambda j, i=i: xin[j % len(xin)]) if (i == 0 and xin) else (lambda j, i=i: b["a"][i][:rows])
             calls.append((f"forward L{i + 1} {k}->{n}", i == 0 and bool(xin),
@@ -355,9 +363,10 @@ def kernel_roofline(tr, xs, ys, dtype, steps, device, use_graph):
                           lambda j, i=i, p=p, src=src: ops.dense_backward_dw_sgd(
                               src(j), b["dz"][i][:rows], p["weights"], p["biases"], 0.0, w_shadow=L._shadow[i],
                               workspace=L._ws)))
-        calls.append((f"softmax-CE N={L.layer_params[-1]['weights'].shape[1]}", False,
-                      lambda j: ops.softmax_ce(b["a"][-1][:rows], ys[j % len(ys)], b["dz"][-1][:rows],
-                                               b["row_loss"][:rows], b["loss"], 1.0 / rows)))
+        if not fused_out:
+            calls.append((f"softmax-CE N={L.layer_params[-1]['weights'].shape[1]}", False,
+                          lambda j: ops.softmax_ce(b["a"][-1][:rows], ys[j % len(ys)], b["dz"][-1][:rows],
+                                                   b["row_loss"][:rows], b["loss"], 1.0 / rows)))
         for name, rotates, fn in calls:
             graphs = []
             for j in range(len(xs) if rotates else 1):

@@ -220,7 +220,9 @@ struct Cfg {
   static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr uint32_t TMEM_COLS = 2 * BN;
   static constexpr uint32_t STG_PITCH = 36;                       // floats per staged row (16-B aligned, conflict-free)
-  static constexpr uint32_t STG_BYTES = 4 * 32 * STG_PITCH * 4;   // one 32x32 fp32 transpose buffer per epilogue warp
+  static constexpr uint32_t STG_WARP = 32 * STG_PITCH + BN;       // floats per epilogue warp: 32x32 transpose buffer + the
+                                                                  // tile's BN bias values
+  static constexpr uint32_t STG_BYTES = 4 * STG_WARP * 4;
   static constexpr uint32_t BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
   static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES;
 };
@@ -257,26 +259,30 @@ __device__ __forceinline__ TileCoord decode_tile(int tile, const UmmaParams& p) 
 // c+1 is in flight while chunk c is processed, and the global operand loads of a chunk (bias / A_prev /
 // W_master) are issued before its transpose.
 template <int BN, int EPI>
-__device__ __forceinline__ void epilogue_chunk(const UmmaParams& p, float* stg, const float (&v)[32], int nrows,
-                                               int64_t idx0, int col, int lane) {
+__device__ __forceinline__ void epilogue_load_aprev(const UmmaParams& p, uint4 (&ap)[4], int nrows, int64_t idx0, int col,
+                                                    int lane) {
+  const int r8 = lane >> 2;
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int r = it * 8 + r8;
+    ap[it] = make_uint4(0, 0, 0, 0);
+    if (EPI == EPI_DX && col < p.N && p.act != DDNN_ACT_LINEAR && r < nrows)
+      ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
+  }
+}
+
+// `ap`: EPI_DX, 8 bf16 of A_prev for each of the lane's 4 rows, loaded one chunk ahead by the caller.
+// `bias_s`: EPI_FWD_*, the tile's bias values staged in shared memory (index = column inside the tile).
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_chunk(const UmmaParams& p, float* stg, const float* bias_s, const float (&v)[32],
+                                               const uint4 (&ap)[4], int nrows, int64_t idx0, int col, int tcol, int lane) {
   const int cg = lane & 3, r8 = lane >> 2;
   const bool in = col < p.N;  // N % 8 == 0: a group of 8 columns is all in or all out
-  float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
-  uint4 ap[4];          // EPI_DX: 8 bf16 of A_prev per row
   float4 w0[4], w1[4];  // EPI_SGD: 8 fp32 of W_master per row
   if (in) {
-    if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
-      b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-      b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col + 4));
-    }
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const int r = it * 8 + r8;
-      if (EPI == EPI_DX) {
-        ap[it] = make_uint4(0, 0, 0, 0);
-        if (p.act != DDNN_ACT_LINEAR && r < nrows)
-          ap[it] = *reinterpret_cast<const uint4*>(p.aprev + idx0 + (int64_t)r * p.N);
-      }
       if (EPI == EPI_SGD) {
         w0[it] = w1[it] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (r < nrows) {
@@ -292,6 +298,11 @@ __device__ __forceinline__ void epilogue_chunk(const UmmaParams& p, float* stg, 
         make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
   __syncwarp();
   if (in) {
+    float4 b0 = make_float4(0.f, 0.f, 0.f, 0.f), b1 = b0;
+    if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+      b0 = *reinterpret_cast<const float4*>(bias_s + tcol);
+      b1 = *reinterpret_cast<const float4*>(bias_s + tcol + 4);
+    }
 #pragma unroll
     for (int it = 0; it < 4; ++it) {
       const int r = it * 8 + r8;
@@ -342,6 +353,21 @@ __device__ __forceinline__ void epilogue_chunk(const UmmaParams& p, float* stg, 
   __syncwarp();
 }
 
+// Stages the tile's bias values for this warp (called BEFORE waiting for the accumulator, so the global-load
+// latency hides behind the MMAs of the tile).
+template <int BN, int EPI>
+__device__ __forceinline__ void epilogue_stage_bias(const UmmaParams& p, float* stg, int n0, int lane) {
+  if (EPI == EPI_FWD_BF16 || EPI == EPI_FWD_F32) {
+    float* bias_s = stg + 32 * Cfg<BN>::STG_PITCH;
+#pragma unroll
+    for (int i = 0; i < BN / 32; ++i) {
+      const int c = i * 32 + lane;
+      bias_s[c] = (n0 + c < p.N) ? __ldg(p.bias + n0 + c) : 0.f;
+    }
+    __syncwarp();
+  }
+}
+
 template <int BN, int EPI>
 __device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, uint32_t tmem_acc, int row0, int n0,
                                               int64_t zoff, int q, int lane) {
@@ -350,18 +376,25 @@ __device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, u
   const int cg = lane & 3;
   const uint32_t tbase = tmem_acc + ((uint32_t)(q * 32) << 16);
   const int64_t rbase = ((int64_t)row0 + zoff) * p.N;
+  const float* bias_s = stg + 32 * Cfg<BN>::STG_PITCH;
   float va[32], vb[32];
+  uint4 apa[4], apb[4];
   tmem_ld32(tbase, va);
+  epilogue_load_aprev<BN, EPI>(p, apa, nrows, rbase + n0 + cg * 8, n0 + cg * 8, lane);
 #pragma unroll 1
   for (int c = 0; c < BN / 32; c += 2) {
+    int tcol = c * 32 + cg * 8, col = n0 + tcol;
     tmem_ld_wait();                        // chunk c has landed in va
-    tmem_ld32(tbase + (c + 1) * 32, vb);   // chunk c+1 streams in while chunk c is processed
-    int col = n0 + c * 32 + cg * 8;
-    epilogue_chunk<BN, EPI>(p, stg, va, nrows, rbase + col, col, lane);
+    tmem_ld32(tbase + (c + 1) * 32, vb);   // chunk c+1 (accumulator and A_prev) streams in while chunk c is processed
+    epilogue_load_aprev<BN, EPI>(p, apb, nrows, rbase + col + 32, col + 32, lane);
+    epilogue_chunk<BN, EPI>(p, stg, bias_s, va, apa, nrows, rbase + col, col, tcol, lane);
     tmem_ld_wait();
-    if (c + 2 < BN / 32) tmem_ld32(tbase + (c + 2) * 32, va);
-    col += 32;
-    epilogue_chunk<BN, EPI>(p, stg, vb, nrows, rbase + col, col, lane);
+    if (c + 2 < BN / 32) {
+      tmem_ld32(tbase + (c + 2) * 32, va);
+      epilogue_load_aprev<BN, EPI>(p, apa, nrows, rbase + col + 64, col + 64, lane);
+    }
+    tcol += 32, col += 32;
+    epilogue_chunk<BN, EPI>(p, stg, bias_s, vb, apb, nrows, rbase + col, col, tcol, lane);
   }
 }
 
@@ -471,10 +504,11 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   } else if (warp >= 4) {
     // ===================== epilogue =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
-    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * 32 * C::STG_PITCH;
+    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * C::STG_WARP;
     uint32_t as = 0, aphase = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
       const TileCoord t = decode_tile(tile, p);
+      epilogue_stage_bias<BN, EPI>(p, stg, t.n_blk * BN, lane);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       epilogue_tile<BN, EPI>(p, stg, tmem_base + as * BN, t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
@@ -628,10 +662,11 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   } else if (warp >= 4) {
     // ===================== epilogue (both CTAs, own 128 rows) =====================
     const int q = warp & 3;
-    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * 32 * Cfg<256>::STG_PITCH;
+    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * Cfg<256>::STG_WARP;
     uint32_t as = 0, aphase = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const TileCoord t = decode_tile(tile, p);
+      epilogue_stage_bias<BN, EPI>(p, stg, t.n_blk * BN, lane);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       epilogue_tile<BN, EPI>(p, stg, tmem_base + as * BN, t.m_blk * 256 + (int)rank * BLOCK_M + q * 32, t.n_blk * BN,
