@@ -222,7 +222,8 @@ size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
   size_t umma = 0;
   if (dtype == DDNN_BF16 && umma_shape_ok(B, K, N)) {
     const size_t s2 = (size_t)umma_dw_splits(B, K, N);
-    umma = (s2 > 1 ? s2 * (size_t)K * np : 0) * sizeof(float) + (size_t)colsum_splits(B, N) * np * sizeof(float);
+    const size_t cs = (size_t)colsum_splits(B, N);
+    umma = (s2 > 1 ? s2 * (size_t)K * np : 0) * sizeof(float) + (cs > s2 ? cs : s2) * np * sizeof(float);
   }
   size_t need = simt > umma ? simt : umma;
   if (skinny_ok(K, N)) {
@@ -266,12 +267,16 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
     const int splits = umma_dw_splits(B, K, N);
     float* dw_part = splits > 1 ? ws : nullptr;
     float* db_part = ws + (splits > 1 ? (size_t)splits * K * np : 0);
-    const int cs = colsum_splits(B, N);
+    int cs = colsum_splits(B, N), db_fused = 0;
     rc = umma_dw((const bf16*)X, (const bf16*)dZ, dw_part, splits, W_master, (bf16*)W_shadow, dW_out, lr, apply, B, K,
-                 N, st);
+                 N, db_part, &db_fused, st);
     if (rc) return rc;
-    rc = colsum_partials(dZ, db_part, cs, B, N, dtype, st);
-    if (rc) return rc;
+    if (db_fused) {
+      cs = splits;  // the GEMM wrote one bias-gradient partial per split
+    } else {
+      rc = colsum_partials(dZ, db_part, cs, B, N, dtype, st);
+      if (rc) return rc;
+    }
     if (splits > 1)  // weights (splits) and bias row (cs) reduced in one launch
       return reduce_dw2(dw_part, db_part, splits, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
     return reduce_dw(dw_part, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);

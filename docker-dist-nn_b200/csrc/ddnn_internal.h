@@ -68,8 +68,11 @@ int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int6
             int64_t N, int act_prev, cudaStream_t st);
 // Split-K plan for dW on tcgen05; splits == 1 means the SGD/store epilogue is fused.
 int umma_dw_splits(int64_t B, int64_t K, int64_t N);
+// db_part/db_fused (optional): when the split-K plan puts one tile on every CTA the kernel also writes the
+// bias-gradient partials db_part[split][Np] (ones-operand MMA) and sets *db_fused = 1; otherwise the caller
+// runs colsum_partials.
 int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_master,
             bf16* W_shadow, float* dW_out, float lr, int apply, int64_t B, int64_t K, int64_t N,
-            cudaStream_t st);
+            float* db_part, int* db_fused, cudaStream_t st);
 
 }  // namespace ddnn

@@ -40,6 +40,8 @@ struct UmmaParams {
   float lr;
   int64_t zrows;  // row offset per split for EPI_STORE partials
   uint64_t hint_a, hint_b;  // L2 eviction-priority policies of the A / B operand loads (CTA-pair kernel)
+  float* db_part;  // dW split-K (EPI_STORE, one tile per CTA): column sums of the B operand, [split][db_np]
+  int db_np;
 };
 
 // ---- PTX wrappers -------------------------------------------------------------------
@@ -224,7 +226,8 @@ struct Cfg {
                                                                   // tile's BN bias values
   static constexpr uint32_t STG_BYTES = 4 * STG_WARP * 4;
   static constexpr uint32_t BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES;
+  static constexpr uint32_t ONES_BYTES = 2048;  // all-ones bf16 operand of the fused bias-gradient MMA
+  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 128 + ONES_BYTES;
 };
 
 struct TileCoord {
@@ -437,6 +440,18 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     tmem_alloc(tmem_slot, C::TMEM_COLS);
     tmem_relinquish();
   }
+  // Bias gradient of the split-K dW GEMM on the tensor core: db[n] = sum_r dZ[r][n] = (ones . dZ)[0][n].  The
+  // B tiles (dZ) are in shared memory anyway, so CTAs of m-block 0 issue a second MMA per k-step against an
+  // all-ones A operand into the (otherwise idle: one tile per CTA) second accumulator stage -- no extra pass
+  // over dZ.  All-ones is layout-invariant, so 2 KB (one k-step of one 64-wide MN atom) serves as the whole
+  // 128 x 64 operand: LBO = 0 aliases the MN atoms and the descriptor never advances along k.
+  const uint32_t ones_base = (bars + C::BAR_BYTES + C::STG_BYTES + 127u) & ~127u;
+  const bool fuse_db = EPI == EPI_STORE && A_MN && B_MN && p.db_part != nullptr;
+  if (fuse_db && warp == 3) {
+    uint32_t* o = reinterpret_cast<uint32_t*>(smem_raw + (ones_base - raw));
+    for (int i = lane; i < (int)(C::ONES_BYTES / 4); i += 32) o[i] = 0x3F803F80u;  // two bf16 1.0
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA
+  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -492,6 +507,12 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
             umma_bf16(d_tmem, operand_desc<A_MN>(a_base, k), operand_desc<B_MN>(b_base, k), idesc,
                       (kb > t.kb0 || k > 0) ? 1u : 0u);
+          if (fuse_db && t.m_blk == 0) {
+#pragma unroll
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+              umma_bf16(tmem_base + BN, make_desc(ones_base, 0, 1024), operand_desc<B_MN>(b_base, k), idesc,
+                        (kb > t.kb0 || k > 0) ? 1u : 0u);
+          }
           umma_commit(empty_bar(stage));  // frees the smem slot when these MMAs finish
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -513,6 +534,23 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       tc_fence_after();
       epilogue_tile<BN, EPI>(p, stg, tmem_base + as * BN, t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
                              EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0, q, lane);
+      if (fuse_db && t.m_blk == 0 && q == 0) {
+        // every row of the ones-accumulator holds the column sums; TMEM lane 0 belongs to lane 0 of this warp
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          float v[32];
+          tmem_ld32(tmem_base + BN + c * 32, v);
+          tmem_ld_wait();
+          const int col = t.n_blk * BN + c * 32;
+          if (lane == 0) {
+            float* o = p.db_part + (int64_t)t.ks * p.db_np + col;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (col + 4 * j < p.N)  // N % 8 == 0
+                *reinterpret_cast<float4*>(o + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          }
+        }
+      }
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty_bar(as));
@@ -918,7 +956,9 @@ int umma_dw_splits(int64_t B, int64_t K, int64_t N) {
   const long tiles = (long)cdiv(K, BLOCK_M) * cdiv(N, bn);
   if (tiles >= num_sms()) return 1;
   const int num_kb = cdiv(B, BLOCK_K);
-  long want = (num_sms() + tiles - 1) / tiles;
+  // one wave: tiles x splits <= SMs.  (Rounding up put 154 tiles on 148 CTAs for the 784 x 256 layer: six CTAs
+  // ran two tiles and the kernel took two tile-times.)
+  long want = num_sms() / tiles;
   long max_by_k = num_kb / 4;  // >= 4 k-blocks per split
   if (max_by_k < 1) max_by_k = 1;
   long s = want < max_by_k ? want : max_by_k;
@@ -928,7 +968,8 @@ int umma_dw_splits(int64_t B, int64_t K, int64_t N) {
 }
 
 int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_master, bf16* W_shadow, float* dW_out,
-            float lr, int apply, int64_t B, int64_t K, int64_t N, cudaStream_t st) {
+            float lr, int apply, int64_t B, int64_t K, int64_t N, float* db_part, int* db_fused, cudaStream_t st) {
+  if (db_fused) *db_fused = 0;
   // D[K, N] = X[B, K]^T . dZ[B, N] : GEMM-M = K, GEMM-N = N, reduction = B
   const int bn = pick_bn(N);
   CUtensorMap ta, tb;
@@ -943,6 +984,13 @@ int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_
     }
     p.out = dw_part;
     p.zrows = K;
+    // one tile per CTA (the usual split-K plan): the bias gradient rides along on the idle accumulator stage
+    const long total = (long)p.m_blocks * p.n_blocks * p.splits;
+    if (db_part && db_fused && total <= (long)(num_sms() - g_sm_reserve.load())) {
+      p.db_part = db_part;
+      p.db_np = (int)((N + 3) & ~(int64_t)3);
+      *db_fused = 1;
+    }
     return launch_bn<true, true, EPI_STORE>(bn, ta, tb, p, st);
   }
   if (apply) {
