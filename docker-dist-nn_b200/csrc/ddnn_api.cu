@@ -2,6 +2,7 @@
 // engine (tcgen05 GEMMs for aligned bf16 layers, SIMT kernels otherwise) and launches.
 #include <cstring>
 #include <mutex>
+#include <map>
 #include <set>
 #include <string>
 #include <utility>
@@ -24,14 +25,16 @@ void set_error(const char* fmt, ...) {
 }
 
 int ensure_dynamic_smem(const void* kernel, size_t bytes) {
+  // the attribute is a per-(kernel, device) high-water mark: raise it when a later shape needs more
   static std::mutex mu;
-  static std::set<std::pair<const void*, int>> done;
+  static std::map<std::pair<const void*, int>, size_t> done;
   int dev = 0;
   DDNN_CUDA_CHECK(cudaGetDevice(&dev));
   std::lock_guard<std::mutex> g(mu);
-  if (done.count({kernel, dev})) return DDNN_OK;
+  auto it = done.find({kernel, dev});
+  if (it != done.end() && it->second >= bytes) return DDNN_OK;
   DDNN_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-  done.insert({kernel, dev});
+  done[{kernel, dev}] = bytes;
   return DDNN_OK;
 }
 

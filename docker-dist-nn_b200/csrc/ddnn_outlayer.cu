@@ -237,15 +237,16 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<const uint32_t*>(&h);
 }
 
-__global__ void __launch_bounds__(256, 1)
+template <int ACT>
+__global__ void __launch_bounds__(256, 2)
 outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, const float* __restrict__ bias,
                     const int32_t* __restrict__ labels, bf16* __restrict__ dZ, float* __restrict__ row_loss,
                     bf16* __restrict__ dZprev, float* __restrict__ dw_part, float* __restrict__ db_part, int64_t B,
-                    int K, int N, int np, int act_prev, float inv_denom, int num_tiles) {
+                    int K, int N, int np, float inv_denom, int num_tiles) {
   extern __shared__ __align__(16) uint8_t sm_raw[];
   const int PA = K + 8;  // bf16 per staged A row: (2K + 16) bytes, an odd multiple of 16 B
-  bf16* abuf = reinterpret_cast<bf16*>(sm_raw);            // [2][MT_ROWS][PA]
-  bf16* wk = abuf + 2 * MT_ROWS * PA;                      // [K][WK_PITCH]   W row-major, classes padded
+  bf16* at = reinterpret_cast<bf16*>(sm_raw);              // [MT_ROWS][PA]   the tile of A, later dZprev in place
+  bf16* wk = at + MT_ROWS * PA;                            // [K][WK_PITCH]   W row-major, classes padded
   bf16* dzs = wk + K * WK_PITCH;                           // [MT_ROWS][WK_PITCH]  dZ rounded to bf16
   bf16* dzl = dzs + MT_ROWS * WK_PITCH;                    // [MT_ROWS][WK_PITCH]  the rounding remainder (dW only)
   float* red = reinterpret_cast<float*>(dzl + MT_ROWS * WK_PITCH);  // [8][16]
@@ -253,19 +254,24 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
   const int g = lane >> 2, t = lane & 3;
   const int cpr = K >> 3;  // 16-byte chunks per row
 
-  auto load_tile = [&](int tile, int buf) {
-    const int64_t r0 = (int64_t)tile * MT_ROWS;
-    for (int i = tid; i < MT_ROWS * cpr; i += 256) {
-      const int r = i / cpr, c = i - r * cpr;
-      const bool ok = r0 + r < B;  // rows past the end are zero-filled (src-size 0)
-      cp_async16(sm_u32(abuf + ((size_t)buf * MT_ROWS + r) * PA + c * 8), A + (ok ? (r0 + r) * K + c * 8 : 0),
-                 ok ? 16 : 0);
+  const int wr = warp * 16;  // this warp's first row inside a tile
+  // Every warp stages ITS 16 rows (lane = 16-byte chunk of a row, K <= 256): phases 1 and 3 touch only those,
+  // so the next tile's rows can stream in as soon as the warp has stored its part of this one.  Two CTAs per
+  // SM cover each other's load latency.
+  auto load_rows = [&](int tile) {
+    const int64_t r0 = (int64_t)tile * MT_ROWS + wr;
+    if (lane < cpr) {
+#pragma unroll
+      for (int r = 0; r < 16; ++r) {
+        const bool ok = r0 + r < B;  // rows past the end are zero-filled (src-size 0)
+        cp_async16(sm_u32(at + (wr + r) * PA + lane * 8), A + (ok ? (r0 + r) * K + lane * 8 : 0), ok ? 16 : 0);
+      }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   };
 
   int tile = blockIdx.x;
-  if (tile < num_tiles) load_tile(tile, 0);
+  if (tile < num_tiles) load_rows(tile);
   for (int i = tid; i < K * WK_PITCH; i += 256) {
     const int k = i / WK_PITCH, n = i - k * WK_PITCH;
     wk[i] = n < N ? W[(int64_t)k * N + n] : __float2bfloat16_rn(0.f);
@@ -291,14 +297,11 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
   // per-lane ldmatrix row addresses: matrix j = lane/8 of an x4 load, row i = lane%8
   const int li = lane & 7, j1 = (lane >> 3) & 1, j2 = lane >> 4;
 
-  for (int it = 0; tile < num_tiles; tile += gridDim.x, ++it) {
-    const int buf = it & 1;
+  __syncthreads();  // W is staged
+  for (; tile < num_tiles; tile += gridDim.x) {
     asm volatile("cp.async.wait_group 0;" ::: "memory");
-    __syncthreads();  // tile `it` (and, first time, W) is in shared memory; everyone has left tile it-1
-    if (tile + (int)gridDim.x < num_tiles) load_tile(tile + gridDim.x, buf ^ 1);
-    bf16* at = abuf + (size_t)buf * MT_ROWS * PA;
+    __syncwarp();  // this warp's 16 rows have landed
     const int64_t r0 = (int64_t)tile * MT_ROWS;
-    const int wr = warp * 16;  // this warp's first row inside the tile
 
     // ---------------- phase 1: logits of 16 rows, softmax-CE in the accumulator layout ----------------
     float z[2][4];
@@ -346,7 +349,7 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
       for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          ex[nt][e] = expf(z[nt][e] - m[e >> 1]);  // exp(-inf) = 0 for the padded classes
+          ex[nt][e] = __expf(z[nt][e] - m[e >> 1]);  // arguments <= 0; exp(-inf) = 0 for the padded classes
           s[e >> 1] += ex[nt][e];
           if (nt * 8 + 2 * t + (e & 1) == y[e >> 1]) zy[e >> 1] = z[nt][e];
         }
@@ -359,12 +362,13 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
         if (t == 0 && row[h] < B) row_loss[row[h]] = (y[h] >= 0 && y[h] < N) ? -((zy[h] - m[h]) - logf(s[h])) : 0.f;
       }
       float d[2][4];
+      const float inv[2] = {1.0f / s[0], 1.0f / s[1]};
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt)
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           const int h = e >> 1, c = nt * 8 + 2 * t + (e & 1);
-          d[nt][e] = row[h] < B ? (ex[nt][e] * (1.0f / s[h]) - (c == y[h] ? 1.f : 0.f)) * inv_denom : 0.f;
+          d[nt][e] = row[h] < B ? (ex[nt][e] * inv[h] - (c == y[h] ? 1.f : 0.f)) * inv_denom : 0.f;
           if (!cv[nt][e & 1]) d[nt][e] = 0.f;
           if (dZ && cv[nt][e & 1] && row[h] < B) dZ[row[h] * N + c] = __float2bfloat16_rn(d[nt][e]);
         }
@@ -424,8 +428,8 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
         }
       }
     }
+    __syncthreads();  // every warp has read the whole tile: its rows may now be overwritten
     if (dZprev) {
-      __syncthreads();  // every warp has read the whole tile: its rows may now be overwritten in place
       // ---------------- phase 3: dZprev = (dZ . W^T) * f'(A) for this warp's 16 rows ----------------
       // B operand (k = class, n = feature) from W[feature][class]: plain load, matrices
       // (n 0-7 | 8-15 of a 16-feature group) x (k 0-7 | 8-15)
@@ -450,19 +454,28 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
           __nv_bfloat162* pa = arow + fg * 8 + h * 4;  // (row g, features 16 fg + 8 h + 2t, +1)
           __nv_bfloat162* pb = pa + half_pitch8;       // row g + 8
           const float2 xa = __bfloat1622float2(*pa), xb = __bfloat1622float2(*pb);
-          *pa = __floats2bfloat162_rn(c[h][0] * act_bwd(xa.x, act_prev), c[h][1] * act_bwd(xa.y, act_prev));
-          *pb = __floats2bfloat162_rn(c[h][2] * act_bwd(xb.x, act_prev), c[h][3] * act_bwd(xb.y, act_prev));
+          *pa = __floats2bfloat162_rn(c[h][0] * act_bwd(xa.x, ACT), c[h][1] * act_bwd(xa.y, ACT));
+          *pb = __floats2bfloat162_rn(c[h][2] * act_bwd(xb.x, ACT), c[h][3] * act_bwd(xb.y, ACT));
         }
       }
       __syncwarp();
-      for (int r = 0; r < 16; ++r) {
-        const int64_t row = r0 + wr + r;
-        if (row >= B) break;  // warp-uniform
-        for (int ch = lane; ch < cpr; ch += 32)
-          *reinterpret_cast<uint4*>(dZprev + row * K + ch * 8) =
-              *reinterpret_cast<const uint4*>(at + (wr + r) * PA + ch * 8);
+      if (lane < cpr) {
+        const bf16* src = at + wr * PA + lane * 8;
+        bf16* dst = dZprev + (r0 + wr) * K + lane * 8;
+        const int nr = (int)min((int64_t)16, B - (r0 + wr));  // warp-uniform, may be <= 0 in the ragged last tile
+#pragma unroll
+        for (int r4 = 0; r4 < 16; r4 += 4) {
+          uint4 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) v[u] = *reinterpret_cast<const uint4*>(src + (r4 + u) * PA);
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            if (r4 + u < nr) *reinterpret_cast<uint4*>(dst + (int64_t)(r4 + u) * K) = v[u];
+        }
       }
     }
+    // this warp's rows are free again: stream in its part of the CTA's next tile
+    if (tile + (int)gridDim.x < num_tiles) load_rows(tile + gridDim.x);
   }
 
   // ---------------- split partials of this CTA: dw_part[z][K][np], db_part[z][np] ----------------
@@ -508,12 +521,12 @@ int sm_count() {
 }
 bool use_mma(int64_t K, int dtype) { return dtype == DDNN_BF16 && K >= 16 && K % 16 == 0; }
 size_t mma_smem_bytes(int64_t K) {
-  return (size_t)2 * MT_ROWS * (K + 8) * 2 + (size_t)K * WK_PITCH * 2 + (size_t)2 * MT_ROWS * WK_PITCH * 2 + 8 * 16 * 4;
+  return (size_t)MT_ROWS * (K + 8) * 2 + (size_t)K * WK_PITCH * 2 + (size_t)2 * MT_ROWS * WK_PITCH * 2 + 8 * 16 * 4;
 }
 int mma_grid(int64_t B) {
   const int64_t tiles = cdiv(B, MT_ROWS);
-  const int sms = sm_count();
-  return (int)(tiles < sms ? tiles : sms);
+  const int slots = 2 * sm_count();  // two resident CTAs per SM
+  return (int)(tiles < slots ? tiles : slots);
 }
 
 int rows_per_block(int64_t B) {
@@ -552,12 +565,20 @@ static int outlayer_launch_mma(const void* A, const void* W, const float* bias, 
                                int64_t N, int act_prev, float inv_denom, cudaStream_t st) {
   const int np = (int)((N + 3) & ~(int64_t)3);
   const size_t smem = mma_smem_bytes(K);
-  int rc = ensure_dynamic_smem((const void*)outlayer_mma_kernel, smem);
-  if (rc) return rc;
   const int tiles = (int)cdiv(B, MT_ROWS);
-  outlayer_mma_kernel<<<mma_grid(B), 256, smem, st>>>((const bf16*)A, (const bf16*)W, bias, labels, (bf16*)dZ, row_loss,
-                                                      (bf16*)dZprev, dw_part, db_part, B, (int)K, (int)N, np, act_prev,
-                                                      inv_denom, tiles);
+#define DDNN_OUT_MMA(ACT)                                                                                          \
+  do {                                                                                                             \
+    if (int rc_ = ensure_dynamic_smem((const void*)outlayer_mma_kernel<ACT>, smem)) return rc_;                    \
+    outlayer_mma_kernel<ACT><<<mma_grid(B), 256, smem, st>>>((const bf16*)A, (const bf16*)W, bias, labels, (bf16*)dZ, \
+                                                             row_loss, (bf16*)dZprev, dw_part, db_part, B, (int)K, \
+                                                             (int)N, np, inv_denom, tiles);                        \
+  } while (0)
+  switch (act_prev) {
+    case DDNN_ACT_RELU: DDNN_OUT_MMA(DDNN_ACT_RELU); break;
+    case DDNN_ACT_SIGMOID: DDNN_OUT_MMA(DDNN_ACT_SIGMOID); break;
+    default: DDNN_OUT_MMA(DDNN_ACT_LINEAR); break;
+  }
+#undef DDNN_OUT_MMA
   count_launch();
   DDNN_LAUNCH_CHECK();
   return DDNN_OK;
