@@ -107,8 +107,14 @@ def set_cta_pairs(on: bool) -> None:
     check(lib.ddnn_set_cta_pairs(1 if on else 0))
 
 
-def set_f32_tensor_cores(on: bool) -> None:
-    check(lib.ddnn_set_f32_tensor_cores(1 if on else 0))
+F32_TC_FFMA, F32_TC_MMA_SYNC, F32_TC_TCGEN05 = 0, 1, 2
+F32_TC_DEFAULT = F32_TC_TCGEN05  # DDNN_F32_TC_DEFAULT in include/ddnn.h
+
+
+def set_f32_tensor_cores(mode=None) -> None:
+    """Inner product of the aligned fp32 GEMMs: 0 FFMA, 1 3xTF32 on mma.sync, 2 3xTF32 on tcgen05
+    (``None`` restores the library default)."""
+    check(lib.ddnn_set_f32_tensor_cores(F32_TC_DEFAULT if mode is None else int(mode)))
 
 
 def set_sm_reserve(sms: int) -> None:

@@ -14,6 +14,7 @@ namespace ddnn {
 static thread_local std::string g_err;
 std::atomic<long long> g_launches{0};
 static std::atomic<int> g_engine{DDNN_ENGINE_AUTO};
+static std::atomic<int> g_f32_tc{DDNN_F32_TC_DEFAULT};  // inner product of the fp32 GEMMs, see ddnn_set_f32_tensor_cores
 
 void set_error(const char* fmt, ...) {
   char buf[1024];
@@ -61,6 +62,18 @@ static bool use_umma(int dtype, int64_t B, int64_t K, int64_t N, std::initialize
 }
 
 // Skinny kernels (N <= 16): one coalesced pass over the big operand instead of a 64-wide tile.
+// fp32 operands on tcgen05 (error-compensated TF32): 16-byte aligned rows and pointers, widths >= 32.
+// `red` = length of an un-split reduction: the tensor core adds into its fp32 accumulator with truncation, so
+// the error grows linearly with the chain (measured vs float64: 2.6e-6 at 1024, 1.2e-5 at 4096); chains longer
+// than DDNN_TF32_MAX_CHAIN stay on FFMA (forward / dX) or get more splits (dW).
+static bool use_tf32(int dtype, int64_t B, int64_t K, int64_t N, int64_t red, std::initializer_list<const void*> ptrs) {
+  if (g_engine.load() == DDNN_ENGINE_SIMT || dtype != DDNN_F32 || g_f32_tc.load() != 2) return false;
+  if (!tf32_shape_ok(B, K, N) || red > DDNN_TF32_MAX_CHAIN) return false;
+  for (const void* p : ptrs)
+    if (p && !aligned16(p)) return false;
+  return true;
+}
+
 static bool use_skinny(int64_t K, int64_t N) {
   return g_engine.load() == DDNN_ENGINE_AUTO && skinny_ok(K, N);
 }
@@ -98,8 +111,13 @@ int ddnn_set_cta_pairs(int on) {
   return DDNN_OK;
 }
 
-int ddnn_set_f32_tensor_cores(int on) {
-  simt_set_f32_core(on);
+int ddnn_set_f32_tensor_cores(int mode) {
+  if (mode < 0 || mode > 2) {
+    set_error("ddnn_set_f32_tensor_cores: mode %d is not 0 (FFMA), 1 (mma.sync 3xTF32) or 2 (tcgen05 3xTF32)", mode);
+    return DDNN_ERR_ARG;
+  }
+  g_f32_tc.store(mode);
+  simt_set_f32_core(mode == 1);
   return DDNN_OK;
 }
 
@@ -137,6 +155,8 @@ int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A,
     rc = skinny_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
   else if (use_umma(dtype, B, K, N, {X, W, A}))
     rc = umma_forward((const bf16*)X, (const bf16*)W, bias, A, B, K, N, gemm_act, out_dtype, st);
+  else if (out_dtype == DDNN_F32 && use_tf32(dtype, B, K, N, K, {X, W, A, bias}))
+    rc = tf32_forward((const float*)X, (const float*)W, bias, (float*)A, B, K, N, gemm_act, st);
   else
     rc = simt_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
   if (rc) return rc;
@@ -211,6 +231,9 @@ int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, voi
   if (use_skinny(K, N)) return skinny_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
   if (use_umma(dtype, B, K, N, {dZ, W, Aprev, dZprev}))
     return umma_dx((const bf16*)dZ, (const bf16*)W, (const bf16*)Aprev, (bf16*)dZprev, B, K, N, act_prev, st);
+  // the dX GEMM's output is (B x K) and its reduction runs over N
+  if (use_tf32(dtype, B, N, K, N, {dZ, W, Aprev, dZprev}))
+    return tf32_dx((const float*)dZ, (const float*)W, (const float*)Aprev, (float*)dZprev, B, K, N, act_prev, st);
   return simt_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
 }
 
@@ -229,6 +252,11 @@ size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
     umma = (s2 > 1 ? s2 * (size_t)K * np : 0) * sizeof(float) + (cs > s2 ? cs : s2) * np * sizeof(float);
   }
   size_t need = simt > umma ? simt : umma;
+  if (dtype == DDNN_F32 && tf32_shape_ok(B, K, N)) {
+    const size_t s3 = (size_t)tf32_dw_splits(B, K, N), cs = (size_t)colsum_splits(B, N);
+    const size_t t = (s3 * (size_t)K * np + (cs > s3 ? cs : s3) * np) * sizeof(float);
+    if (t > need) need = t;
+  }
   if (skinny_ok(K, N)) {
     const size_t sk = (size_t)skinny_dw_splits(B, K, N) * ((size_t)K + 1) * np * sizeof(float);
     if (sk > need) need = sk;
@@ -283,6 +311,21 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
     if (splits > 1)  // weights (splits) and bias row (cs) reduced in one launch
       return reduce_dw2(dw_part, db_part, splits, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
     return reduce_dw(dw_part, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+  }
+  if (use_tf32(dtype, B, K, N, 0, {X, dZ, W_master, dW_out})) {
+    const int splits = tf32_dw_splits(B, K, N);
+    int cs = colsum_splits(B, N), db_fused = 0;
+    float* dw_part = ws;
+    float* db_part = ws + (size_t)splits * K * np;
+    rc = tf32_dw_partials((const float*)X, (const float*)dZ, dw_part, splits, B, K, N, db_part, &db_fused, st);
+    if (rc) return rc;
+    if (db_fused) {
+      cs = splits;
+    } else {
+      rc = colsum_partials(dZ, db_part, cs, B, N, dtype, st);
+      if (rc) return rc;
+    }
+    return reduce_dw2(dw_part, db_part, splits, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
   }
   const int splits = simt_dw_splits(B, K, N);
   float* dw_part = ws;

@@ -75,4 +75,17 @@ int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_
             bf16* W_shadow, float* dW_out, float lr, int apply, int64_t B, int64_t K, int64_t N,
             float* db_part, int* db_fused, cudaStream_t st);
 
+// ---- fp32 operands on tcgen05 as error-compensated TF32 (ddnn_tf32.cu) -----------------
+constexpr int64_t DDNN_TF32_MAX_CHAIN = 2048;  // longest reduction accumulated in one TMEM accumulator
+bool tf32_shape_ok(int64_t B, int64_t K, int64_t N);
+int tf32_forward(const float* X, const float* W, const float* bias, float* A, int64_t B, int64_t K, int64_t N,
+                 int act, cudaStream_t st);
+int tf32_dx(const float* dZ, const float* W, const float* Aprev, float* dZprev, int64_t B, int64_t K, int64_t N,
+            int act_prev, cudaStream_t st);
+int tf32_dw_splits(int64_t B, int64_t K, int64_t N);
+// split-K partials dw_part[split][K][Np]; like umma_dw, also writes db_part[split][Np] (*db_fused = 1) when every
+// CTA has one tile, otherwise the caller runs colsum_partials; then reduce_dw2
+int tf32_dw_partials(const float* X, const float* dZ, float* dw_part, int splits, int64_t B, int64_t K,
+                     int64_t N, float* db_part, int* db_fused, cudaStream_t st);
+
 }  // namespace ddnn

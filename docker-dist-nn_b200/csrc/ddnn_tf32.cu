@@ -1,0 +1,487 @@
+// fp32 GEMM family on the 5th-generation tensor cores: error-compensated TF32 ("3xTF32") on
+// tcgen05.mma.kind::tf32 with fp32 accumulators in TMEM.
+//
+// The fp32 path of the reference-parity contract (1e-5 relative) cannot use bf16, and FFMA tops out near
+// 20 TFLOP/s on the MNIST layers.  Every fp32 operand x is split as x = hi + lo with hi = rna_tf32(x) and
+// lo = x - hi (exact in fp32, |lo| <= 2^-11 |x|), and the product is evaluated as
+//     A.B  ~=  A_hi.B_hi  +  (A_lo.B_hi + A_hi.B_lo)            (dropped: A_lo.B_lo ~ 2^-22)
+// with the bracketed correction in its OWN TMEM accumulator, added in the epilogue -- the small terms are not
+// rounded against the large running sum.
+//
+// Pipeline per CTA (persistent, one per SM, 384 threads):
+//   warp 0      TMA producer: raw fp32 A / B tiles (128-byte swizzle, 32 fp32 per row) into the `hi` slots
+//   warps 8-15  converters: rewrite each 16-byte chunk of the stage in place as hi and store lo in the sibling
+//               slot.  The split is elementwise, so it is done on the raw swizzled bytes: no layout math.
+//   warp 1      MMA issuer: 3 x (BLOCK_K / 8) tcgen05.mma per stage
+//   warp 2      TMEM allocator; warps 4-7 epilogue (TMEM -> 32x32 transpose -> fused functor -> 16-byte stores)
+// Same three operand layouts as the bf16 family (descriptor major-ness instead of transposes in memory).
+#include <cuda.h>
+
+#include "ddnn_umma.cuh"
+
+namespace ddnn {
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 32;  // 32 fp32 = 128 bytes = one SWIZZLE_128B row
+constexpr int UMMA_K = 8;    // kind::tf32
+constexpr int NUM_THREADS = 512;
+constexpr int CONV_THREADS = 256;  // warps 8-15
+
+struct Tf32Params {
+  int M, N;
+  int m_blocks, n_blocks, num_kb, splits, kb_per_split, group_m;
+  int64_t zrows;  // row offset per split (split-K partials)
+  float* db_part;  // dW split-K with one tile per CTA: column sums of the B operand, [split][db_np] (else null)
+  int db_np;
+};
+
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accum) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+
+// round-to-nearest (ties away) to the 10-bit tf32 mantissa on the bit pattern: what cvt.rna.tf32.f32 does for
+// finite inputs, without its Inf/NaN special-casing (4 instructions per element in SASS instead of 2)
+__device__ __forceinline__ float rna_tf32(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+
+// K-major tile [rows][32 fp32] (row = 128 B, 8-row swizzle atoms 1024 B apart): step k (8 elements) by 32 bytes.
+// MN-major tile: 32-bit MN-major operands exist only in the SWIZZLE_128B_BASE32B layout (32-byte swizzle units,
+// 4-row period; TMA: CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B).  32-element MN atoms, each [32 k][32 mn] (k row =
+// 128 B, 4 KB per atom = LBO); 4-k groups 512 B apart (SBO); step k (8 rows) by 1024 bytes.
+template <bool MN_MAJOR>
+__device__ __forceinline__ uint64_t tf32_desc(uint32_t tile_base, int k) {
+  if (MN_MAJOR) return make_desc_layout(tile_base + k * (UMMA_K * 128), BLOCK_K * 128, 512, 1u);
+  return make_desc(tile_base + k * (UMMA_K * 4), 0, 1024);
+}
+// Instruction descriptor, kind::tf32: D=f32 [4,6)=1, A=tf32 [7,10)=2, B=tf32 [10,13)=2, majors, N>>3, M>>4.
+template <bool A_MN, bool B_MN, int BN>
+__device__ __forceinline__ constexpr uint32_t tf32_idesc() {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((A_MN ? 1u : 0u) << 15) | ((B_MN ? 1u : 0u) << 16) |
+         ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+}
+
+template <int BN>
+struct TCfg {
+  static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 4;  // 16 KB (one of hi / lo)
+  static constexpr uint32_t B_BYTES = BN * BLOCK_K * 4;
+  // Two rings.  The deep one receives the raw TMA tiles (rewritten in place as `hi`): these GEMMs are small and
+  // latency-bound, so what matters is bytes in flight per SM.  The `lo` halves only live from the conversion of
+  // a k-block to the retirement of its MMAs: two slots.
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;  // [A raw -> hi][B raw -> hi]
+  static constexpr int STAGES = BN == 128 ? 4 : (BN == 64 ? 6 : 7);
+  static constexpr int LO_SLOTS = 2;                          // [A lo][B lo] each
+  static constexpr uint32_t TMEM_COLS = 4 * BN < 32 ? 32 : 4 * BN;  // 2 stages x (main, correction)
+  static constexpr uint32_t STG_PITCH = 36;
+  static constexpr uint32_t STG_BYTES = 4 * 32 * STG_PITCH * 4;
+  static constexpr uint32_t BAR_BYTES = ((3 * STAGES + LO_SLOTS + 4) * 8 + 16 + 15) / 16 * 16;  // keeps stg 16-B aligned
+  static constexpr uint32_t ONES_BYTES = 1024;  // all-ones fp32 A operand of the fused bias-gradient MMA (one k-step)
+  static constexpr size_t SMEM_BYTES =
+      1024 + (size_t)(STAGES + LO_SLOTS) * STAGE_BYTES + BAR_BYTES + STG_BYTES + 128 + ONES_BYTES;
+};
+
+// Epilogue of one 128 x BN tile for the warp owning TMEM lanes [32q, 32q+32): main + correction accumulators,
+// 32x32 transpose through shared memory, then lane = (row r8 = lane/4, 8 consecutive columns) feeds the functor
+// with two 4-column groups per row (N % 4 == 0: a group is all in or all out).
+template <int BN, typename Epi>
+__device__ __forceinline__ void tf32_epilogue(const Epi& epi, int M, int N, float* stg, uint32_t tmem_main,
+                                              uint32_t tmem_corr, int row0, int n0, int64_t zoff, int q, int lane) {
+  const int nrows = min(32, M - row0);  // warp-uniform
+  const int cg = lane & 3, r8 = lane >> 2;
+  const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+#pragma unroll 1
+  for (int c = 0; c < BN / 32; ++c) {
+    float v[32], w[32];
+    tmem_ld32(tmem_main + c * 32 + lane_off, v);
+    tmem_ld32(tmem_corr + c * 32 + lane_off, w);
+    tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(&stg[lane * TCfg<BN>::STG_PITCH + 4 * j]) =
+          make_float4(v[4 * j] + w[4 * j], v[4 * j + 1] + w[4 * j + 1], v[4 * j + 2] + w[4 * j + 2],
+                      v[4 * j + 3] + w[4 * j + 3]);
+    __syncwarp();
+    const int col = n0 + c * 32 + cg * 8;
+#pragma unroll
+    for (int it = 0; it < 4; ++it) {
+      const int r = it * 8 + r8;
+      if (r >= nrows) continue;
+      const float4 x0 = *reinterpret_cast<const float4*>(&stg[r * TCfg<BN>::STG_PITCH + cg * 8]);
+      const float4 x1 = *reinterpret_cast<const float4*>(&stg[r * TCfg<BN>::STG_PITCH + cg * 8 + 4]);
+      if (col < N) epi.apply4((int64_t)row0 + r + zoff, col, x0, 4, true);
+      if (col + 4 < N) epi.apply4((int64_t)row0 + r + zoff, col + 4, x1, 4, true);
+    }
+    __syncwarp();
+  }
+}
+
+template <bool A_MN, bool B_MN, int BN, typename Epi>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 const Tf32Params p, const Epi epi) {
+  using C = TCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  const uint32_t lo_ring = tiles + C::STAGES * C::STAGE_BYTES;
+  const uint32_t bars = lo_ring + C::LO_SLOTS * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };                      // TMA bytes landed
+  auto conv_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };        // hi / lo written (all converter warps)
+  auto empty_bar = [&](int s) { return bars + 8u * (2 * C::STAGES + s); };   // MMAs of the stage retired
+  auto lofree_bar = [&](int u) { return bars + 8u * (3 * C::STAGES + u); };  // MMAs that read lo slot u retired
+  auto tfull_bar = [&](int a) { return bars + 8u * (3 * C::STAGES + C::LO_SLOTS + a); };
+  auto tempty_bar = [&](int a) { return bars + 8u * (3 * C::STAGES + C::LO_SLOTS + 2 + a); };
+  const uint32_t tmem_slot = bars + 8u * (3 * C::STAGES + C::LO_SLOTS + 4);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(conv_bar(s), CONV_THREADS / 32);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int u = 0; u < C::LO_SLOTS; ++u) mbar_init(lofree_bar(u), 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(tfull_bar(a), 1);
+      mbar_init(tempty_bar(a), 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  // Bias gradient of the split-K dW GEMM (A_MN && B_MN, one tile per CTA): db[n] = sum_r dZ[r][n] = (ones . dZ)[0][n]
+  // from the dZ tiles already in shared memory.  All-ones is layout-invariant, so 1 KB (one k-step of one 32-wide
+  // MN atom) stands for the whole 128 x 32 operand: LBO = 0 aliases the MN atoms, the descriptor never advances.
+  const uint32_t ones_base = (bars + C::BAR_BYTES + C::STG_BYTES + 127u) & ~127u;
+  const bool fuse_db = A_MN && B_MN && p.db_part != nullptr;
+  if (fuse_db && warp == 3) {
+    float* o = reinterpret_cast<float*>(smem_raw + (ones_base - raw));
+    for (int i = lane; i < (int)(C::ONES_BYTES / 4); i += 32) o[i] = 1.0f;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord t = decode_tile(tile, p);
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), C::A_BYTES + C::B_BYTES);
+          const uint32_t a_dst = tiles + stage * C::STAGE_BYTES;
+          const uint32_t b_dst = a_dst + C::A_BYTES;
+          if (!A_MN) {
+            tma_load_2d(a_dst, &tma_a, full_bar(stage), kb * BLOCK_K, t.m_blk * BLOCK_M);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BLOCK_M / 32; ++i)
+              tma_load_2d(a_dst + i * (BLOCK_K * 128), &tma_a, full_bar(stage), t.m_blk * BLOCK_M + i * 32,
+                          kb * BLOCK_K);
+          }
+          if (!B_MN) {
+            tma_load_2d(b_dst, &tma_b, full_bar(stage), kb * BLOCK_K, t.n_blk * BN);
+          } else {
+#pragma unroll
+            for (int i = 0; i < BN / 32; ++i)
+              tma_load_2d(b_dst + i * (BLOCK_K * 128), &tma_b, full_bar(stage), t.n_blk * BN + i * 32, kb * BLOCK_K);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = tf32_idesc<A_MN, B_MN, BN>();
+      constexpr uint32_t A_STEP = A_MN ? UMMA_K * 128 : UMMA_K * 4, B_STEP = B_MN ? UMMA_K * 128 : UMMA_K * 4;
+      const uint64_t desc_a = tf32_desc<A_MN>(tiles, 0);                    // A hi slot of stage 0, k-step 0
+      const uint64_t desc_b = tf32_desc<B_MN>(tiles + C::A_BYTES, 0);       // B hi slot of stage 0
+      const uint64_t desc_al = tf32_desc<A_MN>(lo_ring, 0);                 // A lo of slot 0
+      const uint64_t desc_bl = tf32_desc<B_MN>(lo_ring + C::A_BYTES, 0);
+      const uint64_t ones_desc = make_desc_layout(ones_base, 0, 512, 1u);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0, u = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord t = decode_tile(tile, p);
+        mbar_wait(tempty_bar(as), aphase ^ 1);
+        tc_fence_after();
+        const uint32_t d_main = tmem_base + as * (2 * BN), d_corr = d_main + BN;
+        for (int kb = t.kb0; kb < t.kb1; ++kb) {
+          mbar_wait(conv_bar(stage), phase);  // hi / lo of this stage are in place
+          tc_fence_after();
+          // all descriptors of the ring differ only in the 16-byte-granular start-address field
+          const uint64_t so = (uint64_t)((stage * C::STAGE_BYTES) >> 4), lo = (uint64_t)((u * C::STAGE_BYTES) >> 4);
+          const uint64_t ah = desc_a + so, al = desc_al + lo;
+          const uint64_t bh = desc_b + so, bl = desc_bl + lo;
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+            const uint32_t acc = (kb > t.kb0 || k > 0) ? 1u : 0u;
+            const uint64_t ka = (uint64_t)k * (A_STEP >> 4), kbo = (uint64_t)k * (B_STEP >> 4);
+            umma_tf32(d_corr, al + ka, bh + kbo, idesc, acc);
+            umma_tf32(d_corr, ah + ka, bl + kbo, idesc, 1u);
+            umma_tf32(d_main, ah + ka, bh + kbo, idesc, acc);
+            if (fuse_db && t.m_blk == 0) {
+              // bias gradient: (ones . dZ_hi) and (ones . dZ_lo) into the idle second accumulator stage
+              umma_tf32(tmem_base + 2 * BN, ones_desc, bh + kbo, idesc, acc);
+              umma_tf32(tmem_base + 3 * BN, ones_desc, bl + kbo, idesc, acc);
+            }
+          }
+          umma_commit(empty_bar(stage));
+          umma_commit(lofree_bar(u));
+          u ^= 1;
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(tfull_bar(as));
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 8) {
+    // ===================== converters: x -> (hi = rna_tf32(x), lo = x - hi) on the raw stage bytes =====================
+    const int ct = threadIdx.x - 256;  // 0..CONV_THREADS-1
+    constexpr int A_CH = C::A_BYTES / 16, B_CH = C::B_BYTES / 16;
+    constexpr int PER = (A_CH + B_CH + CONV_THREADS - 1) / CONV_THREADS;
+    static_assert(A_CH % CONV_THREADS == 0, "a thread's j-th chunk is in A or in B for all threads alike");
+    uint32_t stage = 0, phase = 0, u = 0, uphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord t = decode_tile(tile, p);
+      for (int kb = t.kb0; kb < t.kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        mbar_wait(lofree_bar(u), uphase ^ 1);  // the MMAs of the k-block that last used this lo slot have retired
+        uint8_t* base = smem_raw + (tiles + stage * C::STAGE_BYTES - raw);
+        uint8_t* lobase = smem_raw + (lo_ring + u * C::STAGE_BYTES - raw);
+        float4 x[PER];
+        // all loads first (PER independent 16-byte loads in flight), then the split, then the stores
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+          const int i = ct + j * CONV_THREADS;
+          const bool is_a = j * CONV_THREADS < A_CH;
+          if (is_a || i < A_CH + B_CH)
+            x[j] = *reinterpret_cast<const float4*>(base + i * 16);  // [A][B] are contiguous in a stage
+        }
+#pragma unroll
+        for (int j = 0; j < PER; ++j) {
+          const int i = ct + j * CONV_THREADS;
+          const bool is_a = j * CONV_THREADS < A_CH;
+          if (is_a || i < A_CH + B_CH) {
+            uint8_t* ph = base + i * 16;
+            float4 h, l;
+            h.x = rna_tf32(x[j].x); h.y = rna_tf32(x[j].y); h.z = rna_tf32(x[j].z); h.w = rna_tf32(x[j].w);
+            l.x = x[j].x - h.x; l.y = x[j].y - h.y; l.z = x[j].z - h.z; l.w = x[j].w - h.w;
+            *reinterpret_cast<float4*>(ph) = h;
+            *reinterpret_cast<float4*>(lobase + i * 16) = l;
+          }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to tcgen05.mma
+        __syncwarp();
+        if (lane == 0) mbar_arrive(conv_bar(stage));
+        u ^= 1;
+        if (u == 0) uphase ^= 1;
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int q = warp & 3;
+    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * 32 * C::STG_PITCH;
+    uint32_t as = 0, aphase = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord t = decode_tile(tile, p);
+      mbar_wait(tfull_bar(as), aphase);
+      tc_fence_after();
+      const uint32_t d_main = tmem_base + as * (2 * BN);
+      tf32_epilogue<BN, Epi>(epi, p.M, p.N, stg, d_main, d_main + BN, t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
+                             (int64_t)t.ks * p.zrows, q, lane);
+      if (fuse_db && t.m_blk == 0 && q == 0) {
+        // every row of the ones-accumulators holds the column sums; TMEM lane 0 belongs to lane 0 of this warp
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          float v[32], w[32];
+          tmem_ld32(tmem_base + 2 * BN + c * 32, v);
+          tmem_ld32(tmem_base + 3 * BN + c * 32, w);
+          tmem_ld_wait();
+          const int col = t.n_blk * BN + c * 32;
+          if (lane == 0) {
+            float* o = p.db_part + (int64_t)t.ks * p.db_np + col;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              if (col + 4 * j < p.N)  // N % 4 == 0
+                *reinterpret_cast<float4*>(o + 4 * j) = make_float4(v[4 * j] + w[4 * j], v[4 * j + 1] + w[4 * j + 1],
+                                                                    v[4 * j + 2] + w[4 * j + 2], v[4 * j + 3] + w[4 * j + 3]);
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(tempty_bar(as));
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---- host side ------------------------------------------------------------------------
+int ctas_available() {
+  int n = umma_num_sms() - umma_sm_reserve();
+  return n < 1 ? 1 : n;
+}
+
+int operand_maps(bool a_mn, const float* A, bool b_mn, const float* Bm, int64_t M, int64_t N, int64_t Kred, int bn,
+                 CUtensorMap* ta, CUtensorMap* tb) {
+  int rc = a_mn ? umma_get_tmap(A, 4, M, Kred, 32, 32, 1, ta) : umma_get_tmap(A, 4, Kred, M, 32, BLOCK_M, 0, ta);
+  if (rc != DDNN_OK) return rc;
+  return b_mn ? umma_get_tmap(Bm, 4, N, Kred, 32, 32, 1, tb) : umma_get_tmap(Bm, 4, Kred, N, 32, bn, 0, tb);
+}
+
+void fill_tiles(Tf32Params& p, int64_t M, int64_t N, int64_t Kred, int bn, int splits) {
+  p.M = (int)M;
+  p.N = (int)N;
+  p.m_blocks = (int)cdiv(M, BLOCK_M);
+  p.n_blocks = (int)cdiv(N, bn);
+  p.num_kb = (int)cdiv(Kred, BLOCK_K);
+  if (splits < 1) splits = 1;
+  p.kb_per_split = (int)cdiv(p.num_kb, splits);
+  p.splits = (int)cdiv(p.num_kb, p.kb_per_split);
+  p.group_m = p.m_blocks;
+  p.zrows = 0;
+  p.db_part = nullptr;
+  p.db_np = 0;
+}
+
+// output-tile width: the widest BN that still gives (nearly) every SM a tile; these GEMMs are small, so
+// parallelism across CTAs matters more than operand reuse inside one
+int pick_bn(int64_t M, int64_t N) {
+  const long mb = cdiv(M, BLOCK_M);
+  const long want = (long)ctas_available() * 4 / 5;
+  if (N >= 128 && mb * cdiv(N, 128) >= want) return 128;
+  if (N >= 64 && mb * cdiv(N, 64) >= want) return 64;
+  return 32;
+}
+
+template <bool A_MN, bool B_MN, int BN, typename Epi>
+int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Params& p, const Epi& epi, cudaStream_t st) {
+  auto kern = tf32_gemm_kernel<A_MN, B_MN, BN, Epi>;
+  if (int rc = ensure_dynamic_smem((const void*)kern, TCfg<BN>::SMEM_BYTES)) return rc;
+  const int total = p.m_blocks * p.n_blocks * p.splits;
+  const int ctas = ctas_available();
+  kern<<<total < ctas ? total : ctas, NUM_THREADS, TCfg<BN>::SMEM_BYTES, st>>>(ta, tb, p, epi);
+  count_launch();
+  DDNN_LAUNCH_CHECK();
+  return DDNN_OK;
+}
+template <bool A_MN, bool B_MN, typename Epi>
+int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Params& p, const Epi& epi,
+              cudaStream_t st) {
+  if (bn == 128) return launch_one<A_MN, B_MN, 128, Epi>(ta, tb, p, epi, st);
+  if (bn == 64) return launch_one<A_MN, B_MN, 64, Epi>(ta, tb, p, epi, st);
+  return launch_one<A_MN, B_MN, 32, Epi>(ta, tb, p, epi, st);
+}
+
+}  // namespace
+
+// TMA needs 16-byte row pitches (widths % 4) and the boxes are 32 elements wide
+bool tf32_shape_ok(int64_t B, int64_t K, int64_t N) {
+  return B > 0 && K >= 32 && N >= 32 && K % 4 == 0 && N % 4 == 0;
+}
+
+int tf32_forward(const float* X, const float* W, const float* bias, float* A, int64_t B, int64_t K, int64_t N, int act,
+                 cudaStream_t st) {
+  // D[B, N] = X[B, K] . W[K, N]: A operand K-major, B operand MN-major (W is [K][N] like grpc_node.py:51)
+  const int bn = pick_bn(B, N);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(false, X, true, W, B, N, K, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  Tf32Params p{};
+  fill_tiles(p, B, N, K, bn, 1);
+  EpiFwd<float> epi{bias, A, N, act};
+  return launch_bn<false, true, EpiFwd<float>>(bn, ta, tb, p, epi, st);
+}
+
+int tf32_dx(const float* dZ, const float* W, const float* Aprev, float* dZprev, int64_t B, int64_t K, int64_t N,
+            int act_prev, cudaStream_t st) {
+  // D[B, K] = dZ[B, N] . W[K, N]^T: both operands K-major (the reduction runs along W's rows)
+  const int bn = pick_bn(B, K);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(false, dZ, false, W, B, K, N, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  Tf32Params p{};
+  fill_tiles(p, B, K, N, bn, 1);
+  EpiDx<float> epi{Aprev, dZprev, K, act_prev};
+  return launch_bn<false, false, EpiDx<float>>(bn, ta, tb, p, epi, st);
+}
+
+static int dw_bn(int64_t N) { return N >= 128 ? 128 : (N >= 64 ? 64 : 32); }
+
+int tf32_dw_splits(int64_t B, int64_t K, int64_t N) {
+  const int bn = dw_bn(N);
+  const long tiles = (long)cdiv(K, BLOCK_M) * cdiv(N, bn);
+  const long num_kb = cdiv(B, BLOCK_K);
+  long want = umma_num_sms() / tiles;  // one wave
+  long max_by_k = num_kb / 2;          // >= 2 k-blocks per split
+  if (max_by_k < 1) max_by_k = 1;
+  long s = want < max_by_k ? want : max_by_k;
+  const long min_by_chain = cdiv(B, DDNN_TF32_MAX_CHAIN);  // accuracy first: bounded accumulation chains
+  if (s < min_by_chain) s = min_by_chain;
+  if (s < 1) s = 1;
+  const long per = cdiv(num_kb, s);
+  return (int)cdiv(num_kb, per);
+}
+
+int tf32_dw_partials(const float* X, const float* dZ, float* dw_part, int splits, int64_t B, int64_t K, int64_t N,
+                     float* db_part, int* db_fused, cudaStream_t st) {
+  if (db_fused) *db_fused = 0;
+  // D[K, N] = X[B, K]^T . dZ[B, N]: both operands MN-major, reduction over the batch; partials [split][K][Np]
+  const int bn = dw_bn(N);
+  CUtensorMap ta, tb;
+  int rc = operand_maps(true, X, true, dZ, K, N, B, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  Tf32Params p{};
+  fill_tiles(p, K, N, B, bn, splits);
+  if (p.splits != splits) {
+    set_error("tf32_dw_partials: split plan mismatch (%d vs %d)", p.splits, splits);
+    return DDNN_ERR_ARG;
+  }
+  p.zrows = K;
+  const int64_t np = (N + 3) & ~(int64_t)3;
+  // one tile per CTA: the bias gradient rides along on the idle accumulator stage
+  if (db_part && db_fused && (long)p.m_blocks * p.n_blocks * p.splits <= (long)ctas_available()) {
+    p.db_part = db_part;
+    p.db_np = (int)np;
+    *db_fused = 1;
+  }
+  EpiStoreF32 epi{dw_part, np};
+  return launch_bn<true, true, EpiStoreF32>(bn, ta, tb, p, epi, st);
+}
+
+}  // namespace ddnn

@@ -15,7 +15,7 @@
 #include <mutex>
 #include <unordered_map>
 
-#include "ddnn_internal.h"
+#include "ddnn_umma.cuh"
 
 namespace ddnn {
 namespace {
@@ -44,160 +44,6 @@ struct UmmaParams {
   int db_np;
 };
 
-// ---- PTX wrappers -------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred P1;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
-      "@P1 bra DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "DONE:\n"
-      "}\n" ::"r"(bar), "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-
-__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
-  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tmem_relinquish() {
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
-__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
-
-// D[tmem] (+)= A[smem] . B[smem]   (bf16 x bf16 -> fp32), issued by ONE thread for the CTA
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(d_tmem),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
-      : "memory");
-}
-// arrives on `bar` when all previously issued tcgen05.mma of this thread have completed
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-}
-
-// 32 lanes x 32 columns of fp32: thread i of the warp gets TMEM lane (base_lane + i), columns c..c+31
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
-  uint32_t* r = reinterpret_cast<uint32_t*>(v);
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(taddr)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
-
-// ---- cta_group::2 (CTA pair) wrappers -------------------------------------------------
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-  uint32_t r;
-  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-  return r;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-// TMA load executed by either CTA of the pair; the transaction bytes are credited to the barrier at the
-// same offset in CTA 0 (peer bit 24 of the shared::cluster address cleared).
-__device__ __forceinline__ void tma_load_2d_pair(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1,
-                                                 uint64_t hint) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint "
-      "[%0], [%1, {%3, %4}], [%2], %5;" ::"r"(dst),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(bar & 0xFEFFFFFFu), "r"(c0), "r"(c1), "l"(hint)
-      : "memory");
-}
-__device__ __forceinline__ void tmem_alloc_pair(uint32_t dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
-}
-__device__ __forceinline__ void tmem_relinquish_pair() {
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
-}
-// D[tmem of both CTAs] (+)= A . B with M = 256 over the pair; issued by ONE thread of CTA 0
-__device__ __forceinline__ void umma_bf16_pair(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
-                                               uint32_t accum) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "setp.ne.b32 p, %4, 0;\n"
-      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n"
-      "}\n" ::"r"(d_tmem),
-      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accum)
-      : "memory");
-}
-// arrives (once all previously issued MMAs of this thread are done) on the barrier at this offset in BOTH CTAs
-__device__ __forceinline__ void umma_commit_pair(uint32_t bar) {
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar),
-      "h"((uint16_t)3)
-      : "memory");
-}
-// arrive on the barrier at the same offset in CTA `rank` of the cluster.  Default semantics (release at CTA
-// scope, like a local arrive): the accumulator hand-over is ordered by tcgen05.fence::before_thread_sync, and
-// a cluster-scope release would make the lane wait for all of its outstanding global stores (MEMBAR) per tile.
-__device__ __forceinline__ void mbar_arrive_remote(uint32_t bar, uint32_t rank) {
-  asm volatile(
-      "{\n"
-      ".reg .b32 ra;\n"
-      "mapa.shared::cluster.u32 ra, %0, %1;\n"
-      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n"
-      "}\n" ::"r"(bar),
-      "r"(rank)
-      : "memory");
-}
-
-// ---- descriptors --------------------------------------------------------------------
-// Shared-memory matrix descriptor (sm_100): start>>4 [0,14) | LBO>>4 [16,30) | SBO>>4 [32,46) |
-// version=1 [46,48) | layout [61,64) (2 = SWIZZLE_128B).
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-  uint64_t d = 0;
-  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
-  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
-  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
-  d |= 1ull << 46;
-  d |= 2ull << 61;
-  return d;
-}
 // K-major tile [rows][64] (row = 128 B, 8-row swizzle atoms 1024 B apart): step k by 32 bytes.
 // MN-major tile: 64-element MN atoms, each [64 k][64 mn] (k row = 128 B): 8-k groups 1024 B apart
 // (SBO), MN atoms 8192 B apart (LBO); step k (16 rows) by 2048 bytes.
@@ -229,26 +75,6 @@ struct Cfg {
   static constexpr uint32_t ONES_BYTES = 2048;  // all-ones bf16 operand of the fused bias-gradient MMA
   static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + STG_BYTES + 128 + ONES_BYTES;
 };
-
-struct TileCoord {
-  int m_blk, n_blk, ks, kb0, kb1;
-};
-__device__ __forceinline__ TileCoord decode_tile(int tile, const UmmaParams& p) {
-  TileCoord t;
-  const int per_split = p.m_blocks * p.n_blocks;
-  t.ks = tile / per_split;
-  const int rem = tile - t.ks * per_split;
-  const int group_sz = p.group_m * p.n_blocks;
-  const int gid = rem / group_sz;
-  const int first_m = gid * p.group_m;
-  const int gm = min(p.m_blocks - first_m, p.group_m);
-  const int in_g = rem - gid * group_sz;
-  t.m_blk = first_m + in_g % gm;
-  t.n_blk = in_g / gm;
-  t.kb0 = t.ks * p.kb_per_split;
-  t.kb1 = min(p.num_kb, t.kb0 + p.kb_per_split);
-  return t;
-}
 
 // Epilogue of one 128 x BN accumulator tile for the warp owning TMEM lanes [32q, 32q+32).
 // row0 = first output row of this warp, n0 = first output column of the tile.
@@ -747,8 +573,9 @@ struct TmapKey {
   const void* ptr;
   uint64_t inner, outer;
   uint32_t b0, b1;
+  int elt;  // element bytes | swizzle32 << 8
   bool operator==(const TmapKey& o) const {
-    return ptr == o.ptr && inner == o.inner && outer == o.outer && b0 == o.b0 && b1 == o.b1;
+    return ptr == o.ptr && inner == o.inner && outer == o.outer && b0 == o.b0 && b1 == o.b1 && elt == o.elt;
   }
 };
 struct TmapHash {
@@ -756,16 +583,18 @@ struct TmapHash {
     size_t h = std::hash<const void*>()(k.ptr);
     h = h * 1000003u ^ std::hash<uint64_t>()(k.inner);
     h = h * 1000003u ^ std::hash<uint64_t>()(k.outer);
-    h = h * 1000003u ^ (((size_t)k.b0 << 16) | k.b1);
+    h = h * 1000003u ^ (((size_t)k.b0 << 16) | k.b1) ^ ((size_t)k.elt << 40);
     return h;
   }
 };
 std::mutex g_tmap_mu;
 std::unordered_map<TmapKey, CUtensorMap, TmapHash> g_tmaps;
 
-// bf16 row-major [outer][inner]; box {b0 along inner, b1 along outer}; 128B swizzle; OOB -> 0
-int get_tmap(const bf16* ptr, uint64_t inner, uint64_t outer, uint32_t b0, uint32_t b1, CUtensorMap* out) {
-  TmapKey key{ptr, inner, outer, b0, b1};
+// row-major [outer][inner] of 2-byte (bf16) or 4-byte (fp32) elements; box {b0 along inner, b1 along outer};
+// 128B swizzle; OOB -> 0
+int get_tmap_elt(const void* ptr, int elt, uint64_t inner, uint64_t outer, uint32_t b0, uint32_t b1, int swizzle32,
+                 CUtensorMap* out) {
+  TmapKey key{ptr, inner, outer, b0, b1, elt | (swizzle32 << 8)};
   {
     std::lock_guard<std::mutex> g(g_tmap_mu);
     auto it = g_tmaps.find(key);
@@ -780,12 +609,15 @@ int get_tmap(const bf16* ptr, uint64_t inner, uint64_t outer, uint32_t b0, uint3
     return DDNN_ERR_CUDA;
   }
   cuuint64_t gdim[2] = {inner, outer};
-  cuuint64_t gstride[1] = {inner * sizeof(bf16)};
+  cuuint64_t gstride[1] = {inner * (cuuint64_t)elt};
   cuuint32_t box[2] = {b0, b1};
   cuuint32_t estr[2] = {1, 1};
   CUtensorMap m;
-  CUresult r = enc(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<bf16*>(ptr), gdim, gstride, box, estr,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = enc(&m, elt == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                   const_cast<void*>(ptr), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d) ptr=%p inner=%llu outer=%llu box=%ux%u", (int)r, (const void*)ptr,
@@ -799,6 +631,9 @@ int get_tmap(const bf16* ptr, uint64_t inner, uint64_t outer, uint32_t b0, uint3
   }
   *out = m;
   return DDNN_OK;
+}
+int get_tmap(const bf16* ptr, uint64_t inner, uint64_t outer, uint32_t b0, uint32_t b1, CUtensorMap* out) {
+  return get_tmap_elt(ptr, 2, inner, outer, b0, b1, 0, out);
 }
 
 std::atomic<int> g_sm_reserve{0};
@@ -908,6 +743,13 @@ void fill_tiles(UmmaParams& p, int64_t M, int64_t N, int64_t Kred, int bn, int s
 }
 
 }  // namespace
+
+int umma_get_tmap(const void* ptr, int elt_bytes, uint64_t inner, uint64_t outer, uint32_t b0, uint32_t b1,
+                  int swizzle32, CUtensorMap* out) {
+  return get_tmap_elt(ptr, elt_bytes, inner, outer, b0, b1, swizzle32, out);
+}
+int umma_num_sms() { return num_sms(); }
+int umma_sm_reserve() { return g_sm_reserve.load(); }
 
 void umma_set_pair(int on) { g_use_pair.store(on ? 1 : 0); }
 

@@ -167,9 +167,15 @@ int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
  * per 2-CTA cluster) when a problem has >= 2 waves of such tiles, 0 = always the single-CTA kernel. */
 int ddnn_set_cta_pairs(int on);
 
-/* fp32 path inner product for aligned forward / dW GEMMs: 0 (default) = FFMA, 1 = error-compensated
- * 3xTF32 on the tensor cores (still within the 1e-5 bound; ~4x the FFMA rounding error). */
-int ddnn_set_f32_tensor_cores(int on);
+/* fp32 path inner product for 16-byte-aligned forward / dX / dW GEMMs, all within the 1e-5 bound:
+ *   0 = FFMA (cp.async SIMT kernels);
+ *   1 = error-compensated 3xTF32 on mma.sync fragments inside the SIMT tiling (no faster than FFMA, kept for
+ *       comparison);
+ *   2 = error-compensated 3xTF32 on tcgen05.mma.kind::tf32 (TMA-fed, operands split hi/lo in shared memory by
+ *       converter warps, main and correction accumulators in TMEM), widths >= 32 and % 4 == 0.
+ * The default is DDNN_F32_TC_DEFAULT; other values return DDNN_ERR_ARG. */
+#define DDNN_F32_TC_DEFAULT 2
+int ddnn_set_f32_tensor_cores(int mode);
 
 /* Leaves `sms` SMs free of the persistent tcgen05 GEMM CTAs (default 0).  The pipeline sets this
  * so that NCCL's send/recv kernels, which cannot co-reside with a 210 KB-shared-memory GEMM CTA,

@@ -212,25 +212,34 @@ def test_skinny_output_layer_kernels(cuda_device, bkn, dt):
     assert rel_err(to_np(dx), ref) < (F32_TOL if dt == "f32" else 6e-3)
 
 
-@pytest.mark.parametrize("shape", [(4096, 784, 128), (333, 128, 64), (4096, 64, 128), (1000, 100, 132)])
-@pytest.mark.parametrize("tensor_cores", [True, False])
-def test_f32_inner_product_cores(cuda_device, shape, tensor_cores):
-    """fp32 forward and dW on 16-byte-aligned shapes: the FFMA inner product (default) and the opt-in
-    error-compensated 3xTF32 tensor-core one must both stay within the fp32 bound of the float64 oracle."""
+@pytest.mark.parametrize("shape", [(4096, 784, 128), (333, 128, 64), (4096, 64, 128), (1000, 100, 132),
+                                   (2048, 2048, 256), (777, 36, 32), (5000, 260, 68), (20000, 64, 4096),
+                                   (256, 4096, 64)])
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_f32_inner_product_cores(cuda_device, shape, mode):
+    """fp32 forward, dX and dW on 16-byte-aligned shapes with each inner product: FFMA (0), error-compensated
+    3xTF32 on mma.sync (1) and on tcgen05.mma.kind::tf32 (2, the default: hi/lo operand split in shared memory,
+    correction terms in their own TMEM accumulator).  All must stay within the fp32 bound of the float64 oracle;
+    shapes cover ragged M / N / K tiles (zero-filled TMA boxes), every BN and the split-K dW plan."""
     from ddnn_b200 import _lib, ops
     b, k, n = shape
+    if mode == 1 and max(shape) >= 4096 and shape != (4096, 784, 128) and shape != (4096, 64, 128):
+        pytest.skip("the mma.sync variant has no bound on its accumulation chain (comparison only)")
     x, w, bias = _data(b, k, n, seed=12)
     rng = np.random.default_rng(13)
     dz = rng.standard_normal((b, n)) / b
-    _lib.set_f32_tensor_cores(tensor_cores)
+    a_prev = np.maximum(rng.standard_normal((b, k)), 0.0)
+    _lib.set_f32_tensor_cores(mode)
     try:
         got = ops.dense_forward(to_dev(x), to_dev(w), to_dev(bias), "relu")
         assert rel_err(to_np(got), oracle.activate(np.dot(x, w) + bias, "relu")) < F32_TOL
         dw, db = ops.dense_backward_dw(to_dev(x), to_dev(dz))
         assert rel_err(to_np(dw), np.dot(x.T, dz)) < F32_TOL
         assert rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+        dx = ops.dense_backward_dx(to_dev(dz), to_dev(w), to_dev(a_prev), "relu")
+        assert rel_err(to_np(dx), np.dot(dz, w.T) * (a_prev > 0)) < F32_TOL
     finally:
-        _lib.set_f32_tensor_cores(False)
+        _lib.set_f32_tensor_cores(None)
 
 
 @pytest.mark.parametrize("case", [(4096, 64, 10, "f32", "relu"), (1000, 16, 3, "f32", "sigmoid"),
