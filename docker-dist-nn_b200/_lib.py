@@ -7,6 +7,7 @@ status.  ``SYMBOLS`` lists every entry point ``include/ddnn.h`` declares.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
@@ -29,6 +30,7 @@ SYMBOLS = {
     "ddnn_set_sm_reserve": (C.c_int, [_i32]),
     "ddnn_set_f32_tensor_cores": (C.c_int, [_i32]),
     "ddnn_set_cta_pairs": (C.c_int, [_i32]),
+    "ddnn_set_pdl": (C.c_int, [_i32]),
     "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
     "ddnn_softmax_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp]),
     "ddnn_activate": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp]),
@@ -103,6 +105,11 @@ def set_engine(engine: int) -> None:
     check(lib.ddnn_set_engine(engine))
 
 
+def set_pdl(on: bool) -> None:
+    """Programmatic dependent launch between the kernels of a step (default on)."""
+    check(lib.ddnn_set_pdl(1 if on else 0))
+
+
 def set_cta_pairs(on: bool) -> None:
     check(lib.ddnn_set_cta_pairs(1 if on else 0))
 
@@ -119,3 +126,7 @@ def set_f32_tensor_cores(mode=None) -> None:
 
 def set_sm_reserve(sms: int) -> None:
     check(lib.ddnn_set_sm_reserve(sms))
+
+
+if os.environ.get("DDNN_PDL", "1") == "0":  # A/B switch for measurements
+    set_pdl(False)

@@ -13,6 +13,7 @@ namespace ddnn {
 
 static thread_local std::string g_err;
 std::atomic<long long> g_launches{0};
+std::atomic<int> g_pdl{1};
 static std::atomic<int> g_engine{DDNN_ENGINE_AUTO};
 static std::atomic<int> g_f32_tc{DDNN_F32_TC_DEFAULT};  // inner product of the fp32 GEMMs, see ddnn_set_f32_tensor_cores
 
@@ -103,6 +104,11 @@ int ddnn_set_engine(int engine) {
   }
   g_engine.store(engine);
   outlayer_set_tensor_cores(engine != DDNN_ENGINE_SIMT);  // SIMT pins the fused output layer to its FFMA variant
+  return DDNN_OK;
+}
+
+int ddnn_set_pdl(int on) {
+  g_pdl.store(on ? 1 : 0);
   return DDNN_OK;
 }
 

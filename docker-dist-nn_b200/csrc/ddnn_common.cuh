@@ -40,6 +40,34 @@ inline void count_launch(int n = 1) { g_launches.fetch_add(n, std::memory_order_
 
 inline int cdiv(int64_t a, int64_t b) { return (int)((a + b - 1) / b); }
 
+// ---- programmatic dependent launch ----------------------------------------------------
+// A train step is a chain of short kernels (MNIST: ten of 5-25 us), so the launch latency and the prologue of
+// kernel i+1 are worth hiding behind kernel i.  Kernels launched through launch_pdl() may start as soon as every
+// CTA of their predecessor in the stream has executed pdl_launch_dependents(); they MUST execute pdl_wait()
+// before their first global-memory access (it returns once the predecessor grid has completed and flushed).
+// Both instructions are no-ops in a kernel launched without the attribute.  ddnn_set_pdl(0) turns the attribute
+// off (plain stream order).
+extern std::atomic<int> g_pdl;
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+#endif
+
 // Opts a kernel into `bytes` of dynamic shared memory once per (kernel, device): function attributes
 // belong to the device's context, and one process may drive several GPUs.
 int ensure_dynamic_smem(const void* kernel, size_t bytes);

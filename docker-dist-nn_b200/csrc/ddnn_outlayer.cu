@@ -46,6 +46,8 @@ outlayer_fused_kernel(const T* __restrict__ A, const T* __restrict__ W, const fl
                       int K, int N, int np, int act_prev, float inv_denom, int rows_per_block) {
   constexpr int E = Chunk<T>::E;
   constexpr int NV = NV4 * 4;
+  pdl_launch_dependents();
+  pdl_wait();  // A comes from the forward GEMM before us, W / bias from the previous step's reducer
   extern __shared__ float ws[];  // permuted W for phase 1: [Kp][WPITCH]
   __shared__ __align__(16) float dzs[TILE_ROWS][16];
   const int Kp = (K + 4 * E - 1) / (4 * E) * (4 * E);
@@ -253,6 +255,8 @@ outlayer_mma_kernel(const bf16* __restrict__ A, const bf16* __restrict__ W, cons
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = lane >> 2, t = lane & 3;
   const int cpr = K >> 3;  // 16-byte chunks per row
+  pdl_launch_dependents();
+  pdl_wait();  // A comes from the forward GEMM before us, W / bias from the previous step's reducer
 
   const int wr = warp * 16;  // this warp's first row inside a tile
   // Every warp stages ITS 16 rows (lane = 16-byte chunk of a row, K <= 256): phases 1 and 3 touch only those,
@@ -569,9 +573,9 @@ static int outlayer_launch_mma(const void* A, const void* W, const float* bias, 
 #define DDNN_OUT_MMA(ACT)                                                                                          \
   do {                                                                                                             \
     if (int rc_ = ensure_dynamic_smem((const void*)outlayer_mma_kernel<ACT>, smem)) return rc_;                    \
-    outlayer_mma_kernel<ACT><<<mma_grid(B), 256, smem, st>>>((const bf16*)A, (const bf16*)W, bias, labels, (bf16*)dZ, \
-                                                             row_loss, (bf16*)dZprev, dw_part, db_part, B, (int)K, \
-                                                             (int)N, np, inv_denom, tiles);                        \
+    DDNN_CUDA_CHECK(launch_pdl(outlayer_mma_kernel<ACT>, dim3(mma_grid(B)), dim3(256), smem, st, (const bf16*)A,   \
+                               (const bf16*)W, bias, labels, (bf16*)dZ, row_loss, (bf16*)dZprev, dw_part, db_part, \
+                               B, (int)K, (int)N, np, inv_denom, tiles));                                         \
   } while (0)
   switch (act_prev) {
     case DDNN_ACT_RELU: DDNN_OUT_MMA(DDNN_ACT_RELU); break;
@@ -596,9 +600,9 @@ static int outlayer_launch(const void* A, const void* W, const float* bias, cons
   const int per_lane = (int)((K / E + 3) / 4);
   const int nv4 = (int)((N + 3) / 4);
 #define DDNN_OUT_LAUNCH(NV, MC)                                                                              \
-  outlayer_fused_kernel<NV, MC, T><<<blocks, 256, smem, st>>>(                                                \
-      (const T*)A, (const T*)W, bias, labels, (T*)dZ, row_loss, (T*)dZprev, dw_part, db_part, B, (int)K, (int)N, \
-      np, act_prev, inv_denom, rpb)
+  DDNN_CUDA_CHECK(launch_pdl(outlayer_fused_kernel<NV, MC, T>, dim3(blocks), dim3(256), smem, st, (const T*)A,  \
+                             (const T*)W, bias, labels, (T*)dZ, row_loss, (T*)dZprev, dw_part, db_part, B, (int)K,  \
+                             (int)N, np, act_prev, inv_denom, rpb))
 #define DDNN_OUT_NV(MC)                        \
   switch (nv4) {                               \
     case 1: DDNN_OUT_LAUNCH(1, MC); break;     \

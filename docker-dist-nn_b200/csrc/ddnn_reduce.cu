@@ -14,6 +14,8 @@ __global__ void __launch_bounds__(256)
 reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db_part, int splits_w, int splits_b,
                  int64_t rows,
                  int np, int N, EpiW ew, EpiB eb, bool vecw, bool vecb, int has_db) {
+  pdl_launch_dependents();
+  pdl_wait();  // the partials come from the previous kernel of the stream
   const int q = np >> 2;
   const int64_t total = (rows + (has_db ? 1 : 0)) * q;
   const int sub = threadIdx.x % G;
@@ -62,6 +64,8 @@ reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db
 template <typename T>
 __global__ void __launch_bounds__(256)
 colsum_kernel(const T* __restrict__ dZ, float* __restrict__ part, int64_t B, int N, int np, int rlen, bool vec) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float4 red[8][32];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int col = blockIdx.x * 128 + lane * 4;
@@ -101,6 +105,8 @@ colsum_kernel(const T* __restrict__ dZ, float* __restrict__ part, int64_t B, int
 // row-loads in flight; 8 warps stride the rows of the split and are combined through shared memory.
 __global__ void __launch_bounds__(256)
 colsum_bf16x8_kernel(const bf16* __restrict__ dZ, float* __restrict__ part, int64_t B, int N, int np, int rlen) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[8][32][9];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + lane * 8;
@@ -173,8 +179,8 @@ int reduce_dw2(const float* dw_part, const float* db_part, int splits, int split
   if (blocks > 148 * 8) blocks = 148 * 8;
   if (blocks < 1) blocks = 1;
 #define DDNN_REDUCE(GG, EW, EB, ew, eb, vw, vb)                                                              \
-  reduce_dw_kernel<GG, EW, EB><<<(unsigned)blocks, 256, 0, st>>>(dw_part, db_part, splits, splits_b, rows, np, (int)N, ew, \
-                                                              eb, vw, vb, has_db)
+  DDNN_CUDA_CHECK(launch_pdl(reduce_dw_kernel<GG, EW, EB>, dim3((unsigned)blocks), dim3(256), 0, st, dw_part, db_part, \
+                             splits, splits_b, rows, np, (int)N, ew, eb, vw, vb, has_db))
   if (apply) {
     EpiSgd ew{W_master, (bf16*)W_shadow, N, lr};
     EpiSgd eb{bias, nullptr, N, lr};
@@ -193,7 +199,6 @@ int reduce_dw2(const float* dw_part, const float* db_part, int splits, int split
   }
 #undef DDNN_REDUCE
   count_launch();
-  DDNN_LAUNCH_CHECK();
   return DDNN_OK;
 }
 
@@ -212,14 +217,15 @@ int colsum_partials(const void* dZ, float* db_part, int splits, int64_t B, int64
   const int rlen = cdiv(B, splits);
   dim3 grid(cdiv(N, 128), splits);
   if (dtype == DDNN_F32) {
-    colsum_kernel<float><<<grid, 256, 0, st>>>((const float*)dZ, db_part, B, (int)N, np, rlen,
-                                               vec_ok((const float*)dZ, N));
+    DDNN_CUDA_CHECK(launch_pdl(colsum_kernel<float>, grid, dim3(256), 0, st, (const float*)dZ, db_part, B, (int)N, np,
+                               rlen, vec_ok((const float*)dZ, N)));
   } else if (dtype == DDNN_BF16 && N % 8 == 0 && reinterpret_cast<uintptr_t>(dZ) % 16 == 0) {
     dim3 grid8(cdiv(N, 256), splits);
-    colsum_bf16x8_kernel<<<grid8, 256, 0, st>>>((const bf16*)dZ, db_part, B, (int)N, np, rlen);
+    DDNN_CUDA_CHECK(launch_pdl(colsum_bf16x8_kernel, grid8, dim3(256), 0, st, (const bf16*)dZ, db_part, B, (int)N, np,
+                               rlen));
   } else if (dtype == DDNN_BF16) {
-    colsum_kernel<bf16><<<grid, 256, 0, st>>>((const bf16*)dZ, db_part, B, (int)N, np, rlen,
-                                              vec_ok((const bf16*)dZ, N));
+    DDNN_CUDA_CHECK(launch_pdl(colsum_kernel<bf16>, grid, dim3(256), 0, st, (const bf16*)dZ, db_part, B, (int)N, np,
+                               rlen, vec_ok((const bf16*)dZ, N)));
   } else {
     set_error("colsum: unsupported dtype %d", dtype);
     return DDNN_ERR_UNSUPPORTED;

@@ -123,6 +123,8 @@ softmax_block_kernel(const float* __restrict__ Z, const int32_t* __restrict__ la
 // loss (+)= scale * sum(row_loss) -- single CTA, fixed summation tree => deterministic
 __global__ void __launch_bounds__(1024)
 loss_reduce_kernel(const float* __restrict__ row_loss, float* __restrict__ loss, int64_t B, float scale, int accumulate) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float sh[32];
   float s = 0.f;
   for (int64_t i = threadIdx.x; i < B; i += 1024) s += row_loss[i];
@@ -200,17 +202,15 @@ int softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ, float*
   }
   if (rc != DDNN_OK) return rc;
   if (loss && row_loss) {
-    loss_reduce_kernel<<<1, 1024, 0, st>>>(row_loss, loss, B, inv_denom, accumulate);
+    DDNN_CUDA_CHECK(launch_pdl(loss_reduce_kernel, dim3(1), dim3(1024), 0, st, row_loss, loss, B, inv_denom, accumulate));
     count_launch();
-    DDNN_LAUNCH_CHECK();
   }
   return DDNN_OK;
 }
 
 int loss_reduce(const float* row_loss, float* loss, int64_t B, float scale, int accumulate, cudaStream_t st) {
-  loss_reduce_kernel<<<1, 1024, 0, st>>>(row_loss, loss, B, scale, accumulate);
+  DDNN_CUDA_CHECK(launch_pdl(loss_reduce_kernel, dim3(1), dim3(1024), 0, st, row_loss, loss, B, scale, accumulate));
   count_launch();
-  DDNN_LAUNCH_CHECK();
   return DDNN_OK;
 }
 

@@ -145,6 +145,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+  pdl_launch_dependents();  // the next kernel of the stream may set up while this one runs
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -181,6 +182,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();  // barriers, TMEM and descriptors are ready: now wait for the producer of our operands
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -395,9 +397,9 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Params& p
   if (int rc = ensure_dynamic_smem((const void*)kern, TCfg<BN>::SMEM_BYTES)) return rc;
   const int total = p.m_blocks * p.n_blocks * p.splits;
   const int ctas = ctas_available();
-  kern<<<total < ctas ? total : ctas, NUM_THREADS, TCfg<BN>::SMEM_BYTES, st>>>(ta, tb, p, epi);
+  DDNN_CUDA_CHECK(launch_pdl(kern, dim3(total < ctas ? total : ctas), dim3(NUM_THREADS), TCfg<BN>::SMEM_BYTES, st, ta,
+                             tb, p, epi));
   count_launch();
-  DDNN_LAUNCH_CHECK();
   return DDNN_OK;
 }
 template <bool A_MN, bool B_MN, typename Epi>

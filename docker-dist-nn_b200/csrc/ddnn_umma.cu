@@ -246,6 +246,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+  pdl_launch_dependents();  // the next kernel of the stream may set up while this one runs
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -282,6 +283,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();  // barriers, TMEM and descriptors are ready: now wait for the producer of our operands
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -434,6 +436,7 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
   // p.m_blocks counts 256-row blocks here
   const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tma_a);
@@ -458,6 +461,7 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   cluster_sync_all();  // both CTAs' barriers and TMEM exist before anything crosses the pair
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
@@ -659,9 +663,8 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p
   int ctas = num_sms() - g_sm_reserve.load();
   if (ctas < 1) ctas = 1;
   const int grid = total < ctas ? total : ctas;
-  kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, st>>>(ta, tb, p);
+  DDNN_CUDA_CHECK(launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), Cfg<BN>::SMEM_BYTES, st, ta, tb, p));
   count_launch();
-  DDNN_LAUNCH_CHECK();
   return DDNN_OK;
 }
 
@@ -691,13 +694,15 @@ int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cuda
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = Cfg2::SMEM_BYTES;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = 2;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 2 : 1;
   DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
   count_launch();
   return DDNN_OK;

@@ -163,6 +163,11 @@ size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dt
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);
 
+/* 1 (default) = launch the kernels of a train step with programmatic dependent launch (the next kernel's launch
+ * and prologue overlap the tail of the previous one; every such kernel waits for its predecessor's completion
+ * before its first global-memory access), 0 = plain stream order.  No reference counterpart. */
+int ddnn_set_pdl(int on);
+
 /* bf16 tcgen05 GEMMs: 1 (default) = use the CTA-pair kernel (tcgen05.mma.cta_group::2, 256x256 tile
  * per 2-CTA cluster) when a problem has >= 2 waves of such tiles, 0 = always the single-CTA kernel. */
 int ddnn_set_cta_pairs(int on);
