@@ -360,7 +360,11 @@ int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels,
     set_error("ddnn_output_layer_train: null pointer");
     return DDNN_ERR_ARG;
   }
-  if (apply ? !W_master : (!dW_out || !db_out)) {
+  if (apply < 0 || apply > DDNN_OUTLAYER_DEFER) {
+    set_error("ddnn_output_layer_train: apply = %d", apply);
+    return DDNN_ERR_ARG;
+  }
+  if (apply != DDNN_OUTLAYER_DEFER && (apply ? !W_master : (!dW_out || !db_out))) {
     set_error("ddnn_output_layer_train: missing %s", apply ? "W_master" : "dW_out/db_out");
     return DDNN_ERR_ARG;
   }
@@ -386,6 +390,42 @@ int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels,
   rc = outlayer_fused(A, W, bias, labels, dZ, row_loss, dZprev, dw_part, db_part, B, K, N, act_prev, inv_denom, dtype,
                       st);
   if (rc) return rc;
+  if (apply == DDNN_OUTLAYER_DEFER) return DDNN_OK;  // ddnn_output_layer_finish reduces, on any stream
+  if (loss) {
+    rc = loss_reduce(row_loss, loss, B, inv_denom, accumulate_loss, st);
+    if (rc) return rc;
+  }
+  return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
+}
+
+int ddnn_output_layer_finish(const float* row_loss, float* loss, float* W_master, void* W_shadow, float* bias,
+                             float* dW_out, float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N,
+                             float inv_denom, int accumulate_loss, int dtype, void* workspace,
+                             size_t workspace_bytes, void* stream) {
+  int rc = check_dims("ddnn_output_layer_finish", B, K, N);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (apply != 0 && apply != 1) {
+    set_error("ddnn_output_layer_finish: apply = %d", apply);
+    return DDNN_ERR_ARG;
+  }
+  if (!row_loss || !bias || (apply ? !W_master : (!dW_out || !db_out))) {
+    set_error("ddnn_output_layer_finish: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (!outlayer_fused_ok(nullptr, K, N, dtype)) {
+    set_error("ddnn_output_layer_finish: shape K=%lld N=%lld is not a fused output layer", (long long)K, (long long)N);
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  const size_t need = ddnn_output_layer_workspace_bytes(B, K, N, dtype);
+  if (!workspace || workspace_bytes < need || !aligned16(workspace)) {
+    set_error("ddnn_output_layer_finish: workspace %zu bytes < %zu required (or misaligned)", workspace_bytes, need);
+    return DDNN_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int splits = outlayer_splits(B, K, dtype);
+  float* dw_part = (float*)workspace;
+  float* db_part = dw_part + (size_t)splits * K * np_of(N);
   if (loss) {
     rc = loss_reduce(row_loss, loss, B, inv_denom, accumulate_loss, st);
     if (rc) return rc;

@@ -225,6 +225,9 @@ class Layer:
         # second workspace: the side-stream dW GEMMs of backward_and_step must not share scratch with dW_1
         ws2 = max([ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp[1:]],
                   default=0)
+        # ... and it holds the output layer's split partials when their reduction is deferred to the side stream
+        ws2 = max(ws2, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0], lp[-1]["weights"].shape[1],
+                                                        cdt))
         self._ws_side = torch.empty((max(ws2, 256),), dtype=torch.uint8, device=dev)
         self._rows = rows
         self._gen += 1
@@ -373,10 +376,16 @@ class Layer:
         return ops.output_layer_supported(self._bufs["a"][-2], k, n)
 
     def output_layer_step(self, labels: torch.Tensor, lr: float, rows: Optional[int] = None,
-                          denom: Optional[int] = None, need_input_grad: bool = True) -> torch.Tensor:
+                          denom: Optional[int] = None, need_input_grad: bool = True,
+                          side: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
         """Forward + softmax-CE + dX + dW/db + SGD of the output layer in one pass over its input
         (``ddnn_output_layer_train``).  Call after ``forward_train(..., skip_last=True)``; fills dZ of the
-        layer below (already multiplied by that layer's activation derivative) and the device loss."""
+        layer below (already multiplied by that layer's activation derivative) and the device loss.
+
+        With ``side`` the loss reduction and the split-K reduction + update run on that stream
+        (``ddnn_output_layer_finish``): the dX chain below only needs dZprev, so they leave the critical
+        path.  The caller joins ``side`` before it reads the loss or runs the next step
+        (``backward_and_step`` does)."""
         rows = self._rows if rows is None else rows
         b = self._bufs
         i = len(self.layer_params) - 1
@@ -388,11 +397,23 @@ class Layer:
         elif need_input_grad:
             dz_prev = b["dx"][:rows]
         k_, n_ = p["weights"].shape
+        inv = 1.0 / float(rows if denom is None else denom)
+        main = torch.cuda.current_stream(self.device)
+        if side is None or side == main:
+            with self._span(f"output layer fused {k_}->{n_}"):
+                ops.output_layer_train(b["a"][i][:rows], self._w(i), labels, b["row_loss"][:rows], b["loss"], inv,
+                                       prev_act, self._ws, w_master=p["weights"], bias=p["biases"], lr=lr,
+                                       w_shadow=self._shadow[i], dz=b["dz"][i][:rows], dz_prev=dz_prev)
+            return b["loss"]
         with self._span(f"output layer fused {k_}->{n_}"):
-            ops.output_layer_train(b["a"][i][:rows], self._w(i), labels, b["row_loss"][:rows], b["loss"],
-                                   1.0 / float(rows if denom is None else denom), prev_act, self._ws,
-                                   w_master=p["weights"], bias=p["biases"], lr=lr, w_shadow=self._shadow[i],
-                                   dz=b["dz"][i][:rows], dz_prev=dz_prev)
+            ops.output_layer_train(b["a"][i][:rows], self._w(i), labels, b["row_loss"][:rows], None, inv, prev_act,
+                                   self._ws_side, bias=p["biases"], dz=b["dz"][i][:rows], dz_prev=dz_prev, defer=True)
+        ev = torch.cuda.Event()
+        ev.record(main)
+        side.wait_event(ev)
+        with torch.cuda.stream(side):
+            ops.output_layer_finish(rows, k_, n_, self._cdt, b["row_loss"][:rows], b["loss"], inv, self._ws_side,
+                                    w_master=p["weights"], bias=p["biases"], lr=lr, w_shadow=self._shadow[i])
         return b["loss"]
 
     def gradients(self, rows: Optional[int] = None):

@@ -158,19 +158,36 @@ def output_layer_train(a: torch.Tensor, w: torch.Tensor, labels: torch.Tensor, r
                        w_master: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, lr: float = 0.0,
                        w_shadow: Optional[torch.Tensor] = None, dz: Optional[torch.Tensor] = None,
                        dz_prev: Optional[torch.Tensor] = None, dw_out: Optional[torch.Tensor] = None,
-                       db_out: Optional[torch.Tensor] = None, accumulate_loss: bool = False) -> None:
-    """Fused skinny output layer: logits + softmax-CE + dX + dW/db (+ SGD when ``w_master`` is given)."""
+                       db_out: Optional[torch.Tensor] = None, accumulate_loss: bool = False,
+                       defer: bool = False) -> None:
+    """Fused skinny output layer: logits + softmax-CE + dX + dW/db (+ SGD when ``w_master`` is given).
+    ``defer=True`` runs the fused kernel only; ``output_layer_finish`` (any stream ordered after this call, same
+    workspace) then reduces the loss and the split partials and applies the update."""
     _req(a, name="a"); _req(w, a.dtype, "w"); _req(labels, torch.int32, "labels")
     _req(row_loss, torch.float32, "row_loss"); _req(bias, torch.float32, "bias")
     b, k = a.shape
     n = w.shape[1]
-    apply = 1 if w_master is not None else 0
+    apply = 2 if defer else (1 if w_master is not None else 0)
     act_id = act_prev if isinstance(act_prev, int) else _lib.activation_id(act_prev)
     with torch.cuda.device(a.device):
         check(lib.ddnn_output_layer_train(_p(a), _p(w), _p(labels), _p(dz), _p(row_loss), _p(loss), _p(dz_prev),
                                           _p(w_master), _p(w_shadow), _p(bias), _p(dw_out), _p(db_out), float(lr),
                                           apply, b, k, n, act_id, float(inv_denom), 1 if accumulate_loss else 0,
                                           _DT[a.dtype], _p(workspace), workspace.numel(), _stream(a)))
+
+
+def output_layer_finish(rows: int, k: int, n: int, dtype: torch.dtype, row_loss: torch.Tensor,
+                        loss: Optional[torch.Tensor], inv_denom: float, workspace: torch.Tensor,
+                        w_master: Optional[torch.Tensor] = None, bias: Optional[torch.Tensor] = None, lr: float = 0.0,
+                        w_shadow: Optional[torch.Tensor] = None, dw_out: Optional[torch.Tensor] = None,
+                        db_out: Optional[torch.Tensor] = None, accumulate_loss: bool = False) -> None:
+    """Second half of ``output_layer_train(..., defer=True)`` on the CURRENT stream of the workspace's device."""
+    _req(row_loss, torch.float32, "row_loss"); _req(bias, torch.float32, "bias")
+    with torch.cuda.device(workspace.device):
+        check(lib.ddnn_output_layer_finish(_p(row_loss), _p(loss), _p(w_master), _p(w_shadow), _p(bias), _p(dw_out),
+                                           _p(db_out), float(lr), 1 if w_master is not None else 0, rows, k, n,
+                                           float(inv_denom), 1 if accumulate_loss else 0, _DT[dtype], _p(workspace),
+                                           workspace.numel(), _stream(workspace)))
 
 
 def _workspace(ws: Optional[torch.Tensor], b: int, k: int, n: int, like: torch.Tensor) -> torch.Tensor:

@@ -51,8 +51,9 @@ class Trainer:
         if L.can_fuse_output_layer():
             # skinny output layer: logits, softmax-CE, dX, dW/db and the SGD update in one pass over its input
             L.forward_train(x, 0, skip_last=True)
-            loss = L.output_layer_step(labels, lr, x.shape[0], need_input_grad=False)
+            loss = L.output_layer_step(labels, lr, x.shape[0], need_input_grad=False, side=self._side)
             L.backward_and_step(lr, x.shape[0], side=self._side, top=len(L.layer_params) - 2)
+            torch.cuda.current_stream(self.device).wait_stream(self._side)  # loss + output-layer update are in
             return loss
         L.forward_train(x, 0)
         loss = L.loss_and_grad(labels, 0)

@@ -157,6 +157,21 @@ int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels,
                             float lr, int apply, int64_t B, int64_t K, int64_t N, int act_prev,
                             float inv_denom, int accumulate_loss, int dtype,
                             void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Two-call form: pass apply = DDNN_OUTLAYER_DEFER to ddnn_output_layer_train and it only runs the fused kernel
+ * (row_loss, dZ, dZprev and the split partials in `workspace` are final; *loss and the weights are untouched),
+ * then ddnn_output_layer_finish reduces the loss and the partials and applies SGD / stores the gradients -- on
+ * any stream that is ordered after the first call.  Lets the host take the reduction off the critical path
+ * (dX of the layer below only needs dZprev).  Same B, K, N, dtype and workspace in both calls; the workspace
+ * must not be reused in between.  No reference counterpart.
+ */
+#define DDNN_OUTLAYER_DEFER 2
+int ddnn_output_layer_finish(const float* row_loss, float* loss,
+                             float* W_master, void* W_shadow, float* bias, float* dW_out, float* db_out,
+                             float lr, int apply, int64_t B, int64_t K, int64_t N,
+                             float inv_denom, int accumulate_loss, int dtype,
+                             void* workspace, size_t workspace_bytes, void* stream);
 size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype);
 
 /* out[i] = bf16(in[i]) / fp32(in[i]) converters for staging host-provided fp32 data. */

@@ -294,3 +294,40 @@ def test_fused_output_layer_step(cuda_device, case):
         assert rel_err(to_np(bd), b_before - 0.3 * dz2.sum(axis=0)) < F32_TOL
         if sh is not None:
             assert torch.equal(sh, wm.to(torch.bfloat16))
+
+
+@pytest.mark.parametrize("case", [(4096, 64, 10, "f32"), (20000, 256, 10, "bf16")])
+def test_fused_output_layer_two_call_form(cuda_device, case):
+    """apply = DDNN_OUTLAYER_DEFER + ddnn_output_layer_finish on another stream gives bit-identical weights, bias
+    and loss to the single call."""
+    from ddnn_b200 import ops
+    b, k, n, dt = case
+    tdt = torch.float32 if dt == "f32" else torch.bfloat16
+    rng = np.random.default_rng(31)
+    a = to_dev(np.maximum(rng.standard_normal((b, k)), 0), tdt)
+    w0 = rng.standard_normal((k, n)) / np.sqrt(k)
+    y = to_dev(rng.integers(0, n, size=b), torch.int32)
+    ws = torch.empty(max(256, ops.output_layer_workspace_bytes(b, k, n, tdt)), dtype=torch.uint8, device="cuda")
+    res = []
+    for deferred in (False, True):
+        wm, bias = to_dev(w0), to_dev(np.full(n, 0.01))
+        sh = wm.to(torch.bfloat16) if dt == "bf16" else None
+        row_loss, loss = torch.empty(b, device="cuda"), torch.zeros(1, device="cuda")
+        dxd = torch.empty((b, k), dtype=tdt, device="cuda")
+        wop = sh if dt == "bf16" else wm
+        if not deferred:
+            ops.output_layer_train(a, wop, y, row_loss, loss, 1.0 / b, "relu", ws, w_master=wm, bias=bias, lr=0.1,
+                                   w_shadow=sh, dz_prev=dxd)
+        else:
+            ops.output_layer_train(a, wop, y, row_loss, None, 1.0 / b, "relu", ws, bias=bias, dz_prev=dxd, defer=True)
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                ops.output_layer_finish(b, k, n, tdt, row_loss, loss, 1.0 / b, ws, w_master=wm, bias=bias, lr=0.1,
+                                        w_shadow=sh)
+            torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        res.append((wm.clone(), bias.clone(), loss.clone(), dxd.clone()))
+    for x0, x1 in zip(*res):
+        assert torch.equal(x0, x1)
+    assert not torch.equal(res[0][0], to_dev(w0))  # the update happened
