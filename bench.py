@@ -304,6 +304,10 @@ def _kernel_work(L, rows, dtype):
     # fused skinny output layer: one read of its input, one write of the gradient below it, labels, row losses, dZ
     work[f"output layer fused {k_out}->{n_out}"] = (6.0 * rows * k_out * n_out,
                                                     2 * rows * k_out * elt + rows * 8 + rows * n_out * elt)
+    if n_layers >= 2:  # fused two-layer tail: A1 read once, dZ1 written once (+ labels, row losses)
+        k1, n2 = L.layer_params[-2]["weights"].shape
+        work[f"tail fused {k1}->{n2}->{n_out}"] = (6.0 * rows * (k1 * n2 + n2 * n_out),
+                                                   2 * rows * k1 * elt + rows * 8)
     work[f"softmax-CE N={n_out}"] = (5.0 * rows * n_out, rows * n_out * (4 + elt) + rows * 8)
     return work
 
@@ -342,9 +346,18 @@ def kernel_roofline(tr, xs, ys, dtype, steps, device, use_graph):
         calls = []
         n_layers = len(L.layer_params)
         xin = xs if xs[0].dtype == L.wire_dtype else None  # layer-1 operands straight from the batch pool
-        fused_out = L.can_fuse_output_layer()
+        fused_tail = L.can_fuse_tail2()
+        fused_out = L.can_fuse_output_layer() and not fused_tail
         for i, p in enumerate(L.layer_params):
             k, n = p["weights"].shape
+            if fused_tail and i >= n_layers - 2:  # what train_step launches for the last two layers
+                if i == n_layers - 2:
+                    n3 = L.layer_params[-1]["weights"].shape[1]
+                    calls.append((f"tail fused {k}->{n}->{n3}", False,
+                                  lambda j: L.tail2_kernel(ys[j % len(ys)], rows, ws=L._ws_side)))
+                    calls.append(("tail reducers + SGD (side stream in the step)", False,
+                                  lambda j: L.tail2_finish(0.0, rows, ws=L._ws_side)))
+                continue
             if fused_out and i == n_layers - 1:  # what train_step launches for this layer: one fused entry point
                 calls.append((f"output layer fused {k}->{n}", False,
                               lambda j: L.output_layer_step(ys[j % len(ys)], 0.0, rows)))
@@ -363,7 +376,7 @@ def kernel_roofline(tr, xs, ys, dtype, steps, device, use_graph):
                           lambda j, i=i, p=p, src=src: ops.dense_backward_dw_sgd(
                               src(j), b["dz"][i][:rows], p["weights"], p["biases"], 0.0, w_shadow=L._shadow[i],
                               workspace=L._ws)))
-        if not fused_out:
+        if not fused_out and not fused_tail:
             calls.append((f"softmax-CE N={L.layer_params[-1]['weights'].shape[1]}", False,
                           lambda j: ops.softmax_ce(b["a"][-1][:rows], ys[j % len(ys)], b["dz"][-1][:rows],
                                                    b["row_loss"][:rows], b["loss"], 1.0 / rows)))

@@ -46,6 +46,11 @@ SYMBOLS = {
     "ddnn_output_layer_finish": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64, _f32, _i32,
                                            _i32, _vp, _sz, _vp]),
     "ddnn_output_layer_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
+    "ddnn_tail2_workspace_bytes": (_sz, [_i64, _i64, _i64, _i64, _i32]),
+    "ddnn_tail2_train": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i32, _i32, _i64, _i64, _i64, _i64, _f32,
+                                   _i32, _vp, _sz, _vp]),
+    "ddnn_tail2_finish": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
+                                    _i64, _f32, _i32, _i32, _vp, _sz, _vp]),
     "ddnn_cast_f32_to_bf16": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_cast_bf16_to_f32": (C.c_int, [_vp, _vp, _i64, _vp]),
     "ddnn_ipc_export": (C.c_int, [_vp, _vp, C.POINTER(C.c_int64)]),

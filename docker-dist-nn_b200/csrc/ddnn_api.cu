@@ -433,6 +433,94 @@ int ddnn_output_layer_finish(const float* row_loss, float* loss, float* W_master
   return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
 }
 
+// ---- fused last two layers (ddnn_tail2.cu) ----
+// workspace: [dW2 partials S x K1 x N2][db2 S x N2][dW3 partials S x N2 x Np3][db3 S x Np3]
+struct Tail2Ws {
+  float *dw2, *db2, *dw3, *db3;
+  size_t bytes;
+};
+static Tail2Ws tail2_ws(void* ws, int64_t B, int64_t K1, int64_t N2, int64_t N3) {
+  const size_t S = (size_t)tail2_splits(B), np3 = np_of(N3);
+  Tail2Ws w;
+  w.dw2 = (float*)ws;
+  w.db2 = w.dw2 + S * K1 * N2;
+  w.dw3 = w.db2 + S * N2;
+  w.db3 = w.dw3 + S * N2 * np3;
+  w.bytes = ((S * ((size_t)K1 * N2 + N2 + (size_t)N2 * np3 + np3) * sizeof(float)) + 255) & ~(size_t)255;
+  return w;
+}
+
+size_t ddnn_tail2_workspace_bytes(int64_t B, int64_t K1, int64_t N2, int64_t N3, int dtype) {
+  if (B <= 0 || !tail2_ok(K1, N2, N3, dtype)) return 0;
+  return tail2_ws(nullptr, B, K1, N2, N3).bytes;
+}
+
+int ddnn_tail2_train(const void* A1, const void* W2, const float* b2, const void* W3, const float* b3,
+                     const int32_t* labels, void* dZ1, float* row_loss, int act1, int act2, int64_t B, int64_t K1,
+                     int64_t N2, int64_t N3, float inv_denom, int dtype, void* workspace, size_t workspace_bytes,
+                     void* stream) {
+  int rc = check_dims("ddnn_tail2_train", B, K1, N2);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!tail2_ok(K1, N2, N3, dtype)) {
+    set_error("ddnn_tail2_train: needs fp32, K1 <= 128, N2 <= 64 (both %% 4 == 0), N3 <= 16 (got %lld %lld %lld)",
+              (long long)K1, (long long)N2, (long long)N3);
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  if (!A1 || !W2 || !b2 || !W3 || !b3 || !labels || !row_loss) {
+    set_error("ddnn_tail2_train: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (!aligned16(A1) || (dZ1 && !aligned16(dZ1))) {
+    set_error("ddnn_tail2_train: A1 / dZ1 must be 16-byte aligned");
+    return DDNN_ERR_ARG;
+  }
+  for (int a : {act1, act2})
+    if (a < DDNN_ACT_LINEAR || a >= DDNN_ACT_SOFTMAX) {
+      set_error("ddnn_tail2_train: activation %d is not linear / relu / sigmoid", a);
+      return DDNN_ERR_ACTIVATION;
+    }
+  const Tail2Ws w = tail2_ws(workspace, B, K1, N2, N3);
+  if (!workspace || workspace_bytes < w.bytes || !aligned16(workspace)) {
+    set_error("ddnn_tail2_train: workspace %zu bytes < %zu required (or misaligned)", workspace_bytes, w.bytes);
+    return DDNN_ERR_WORKSPACE;
+  }
+  return tail2_launch((const float*)A1, (const float*)W2, b2, (const float*)W3, b3, labels, (float*)dZ1, row_loss,
+                      w.dw2, w.db2, w.dw3, w.db3, B, K1, N2, N3, act1, act2, inv_denom,
+                      (g_engine.load() != DDNN_ENGINE_SIMT && g_f32_tc.load() != 0) ? 1 : 0, (cudaStream_t)stream);
+}
+
+int ddnn_tail2_finish(const float* row_loss, float* loss, float* W2, float* b2, float* W3, float* b3, float* dW2_out,
+                      float* db2_out, float* dW3_out, float* db3_out, float lr, int apply, int64_t B, int64_t K1,
+                      int64_t N2, int64_t N3, float inv_denom, int accumulate_loss, int dtype, void* workspace,
+                      size_t workspace_bytes, void* stream) {
+  int rc = check_dims("ddnn_tail2_finish", B, K1, N2);
+  if (rc) return rc;
+  if (B == 0) return DDNN_OK;
+  if (!tail2_ok(K1, N2, N3, dtype)) {
+    set_error("ddnn_tail2_finish: unsupported shape / dtype");
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  if (!row_loss || (apply ? (!W2 || !b2 || !W3 || !b3) : (!dW2_out || !db2_out || !dW3_out || !db3_out))) {
+    set_error("ddnn_tail2_finish: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  const Tail2Ws w = tail2_ws(workspace, B, K1, N2, N3);
+  if (!workspace || workspace_bytes < w.bytes || !aligned16(workspace)) {
+    set_error("ddnn_tail2_finish: workspace %zu bytes < %zu required (or misaligned)", workspace_bytes, w.bytes);
+    return DDNN_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  const int S = tail2_splits(B);
+  if (loss) {
+    rc = loss_reduce(row_loss, loss, B, inv_denom, accumulate_loss, st);
+    if (rc) return rc;
+  }
+  rc = reduce_dw(w.dw3, w.db3, S, N2, N3, W3, nullptr, b3, dW3_out, db3_out, lr, apply ? 1 : 0, st);
+  if (rc) return rc;
+  return reduce_dw(w.dw2, w.db2, S, K1, N2, W2, nullptr, b2, dW2_out, db2_out, lr, apply ? 1 : 0, st);
+}
+
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream) {
   if (n <= 0) return DDNN_OK;
   if (!in || !out || !aligned16(in) || (reinterpret_cast<uintptr_t>(out) & 7u)) {

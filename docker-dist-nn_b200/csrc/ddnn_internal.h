@@ -75,6 +75,15 @@ int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_
             bf16* W_shadow, float* dW_out, float lr, int apply, int64_t B, int64_t K, int64_t N,
             float* db_part, int* db_fused, cudaStream_t st);
 
+// ---- fused last two layers of a small fp32 MLP (ddnn_tail2.cu) ----------------------------
+bool tail2_ok(int64_t K1, int64_t N2, int64_t N3, int dtype);
+int tail2_splits(int64_t B);
+int tail2_launch(const float* A1, const float* W2, const float* b2, const float* W3, const float* b3,
+                 const int32_t* labels, float* dZ1, float* row_loss, float* dw2_part, float* db2_part,
+                 float* dw3_part, float* db3_part, int64_t B, int64_t K1, int64_t N2, int64_t N3, int act1,
+                 int act2, float inv_denom, int tensor_cores /* 1: 3xTF32 mma.sync products, 0: FFMA */,
+                 cudaStream_t st);
+
 // ---- fp32 operands on tcgen05 as error-compensated TF32 (ddnn_tf32.cu) -----------------
 constexpr int64_t DDNN_TF32_MAX_CHAIN = 2048;  // longest reduction accumulated in one TMEM accumulator
 bool tf32_shape_ok(int64_t B, int64_t K, int64_t N);

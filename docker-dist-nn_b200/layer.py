@@ -215,6 +215,11 @@ class Layer:
         ws_bytes = max(ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp)
         ws_bytes = max(ws_bytes, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0],
                                                                   lp[-1]["weights"].shape[1], cdt))
+        tail_bytes = 0
+        if len(lp) >= 2 and self.is_output:
+            tail_bytes = ops.tail2_workspace_bytes(rows, lp[-2]["weights"].shape[0], lp[-2]["weights"].shape[1],
+                                                   lp[-1]["weights"].shape[1], cdt)
+        ws_bytes = max(ws_bytes, tail_bytes)
         self._bufs = {
             "cap": rows, "a": a, "dz": dz,
             "dx": torch.empty((rows, lp[0]["weights"].shape[0]), dtype=cdt, device=dev),
@@ -226,8 +231,8 @@ class Layer:
         ws2 = max([ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp[1:]],
                   default=0)
         # ... and it holds the output layer's split partials when their reduction is deferred to the side stream
-        ws2 = max(ws2, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0], lp[-1]["weights"].shape[1],
-                                                        cdt))
+        ws2 = max(ws2, tail_bytes, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0],
+                                                                    lp[-1]["weights"].shape[1], cdt))
         self._ws_side = torch.empty((max(ws2, 256),), dtype=torch.uint8, device=dev)
         self._rows = rows
         self._gen += 1
@@ -244,7 +249,7 @@ class Layer:
         return self._bufs["a"][-1][row0:row0 + rows]
 
     def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None,
-                      out_target: Optional[torch.Tensor] = None, skip_last: bool = False) -> torch.Tensor:
+                      out_target: Optional[torch.Tensor] = None, skip_last: int = 0) -> torch.Tensor:
         """Forward of rows [row0, row0+rows) keeping what backward needs.  ``x`` None means the
         rows are already in ``input_buffer``.  An output node stops at the fp32 logits Z
         (softmax is fused into ``loss_and_grad``).  ``out_target`` (rows, N_last) redirects the
@@ -265,7 +270,7 @@ class Layer:
         n_layers = len(self.layer_params)
         for i, p in enumerate(self.layer_params):
             last = i == n_layers - 1
-            if last and skip_last:  # the fused output-layer step computes the logits itself
+            if i >= n_layers - int(skip_last):  # the fused output-layer (1) / two-layer tail (2) step runs these
                 break
             act = p["activation"]
             if last and self.is_output:
@@ -415,6 +420,61 @@ class Layer:
             ops.output_layer_finish(rows, k_, n_, self._cdt, b["row_loss"][:rows], b["loss"], inv, self._ws_side,
                                     w_master=p["weights"], bias=p["biases"], lr=lr, w_shadow=self._shadow[i])
         return b["loss"]
+
+    def can_fuse_tail2(self) -> bool:
+        """True when the last two local layers (hidden K1 -> N2, output N2 -> N3 with softmax / linear) fit the
+        fused fp32 tail kernel (``ddnn_tail2_train``: K1 <= 128, N2 <= 64, N3 <= 16)."""
+        lp = self.layer_params
+        if not self.is_output or self._bufs is None or len(lp) < 2 or self._cdt != torch.float32:
+            return False
+        if lp[-1]["activation"] in ("relu", "sigmoid") or lp[-2]["activation"] == "softmax":
+            return False
+        act1 = lp[-3]["activation"] if len(lp) > 2 else self.input_activation
+        if act1 == "softmax":
+            return False
+        k1, n2 = lp[-2]["weights"].shape
+        return ops.tail2_workspace_bytes(self._bufs["cap"], k1, n2, lp[-1]["weights"].shape[1], self._cdt) > 0
+
+    def tail2_step(self, labels: torch.Tensor, lr: float, rows: Optional[int] = None, denom: Optional[int] = None,
+                   need_input_grad: bool = True, side: Optional[torch.cuda.Stream] = None) -> torch.Tensor:
+        """Forward, softmax-CE, backward and SGD of the last TWO layers in one kernel plus its reducers.  Call
+        after ``forward_train(..., skip_last=2)``; fills dZ of the layer below them.  With ``side`` the loss
+        reduction, both split-K reductions and the updates run on that stream (the caller joins it)."""
+        main = torch.cuda.current_stream(self.device)
+        deferred = side is not None and side != main
+        ws = self._ws_side if deferred else self._ws
+        self.tail2_kernel(labels, rows, denom, need_input_grad, ws)
+        if deferred:
+            ev = torch.cuda.Event()
+            ev.record(main)
+            side.wait_event(ev)
+        with torch.cuda.stream(side if deferred else main):
+            self.tail2_finish(lr, rows, denom, ws)
+        return self._bufs["loss"]
+
+    def tail2_kernel(self, labels: torch.Tensor, rows: Optional[int] = None, denom: Optional[int] = None,
+                     need_input_grad: bool = True, ws: Optional[torch.Tensor] = None) -> None:
+        """First half of ``tail2_step``: the fused kernel (row losses, dZ below the tail, split partials in ``ws``)."""
+        rows = self._rows if rows is None else rows
+        b, lp = self._bufs, self.layer_params
+        i2 = len(lp) - 2
+        p2, p3 = lp[i2], lp[i2 + 1]
+        act1 = lp[i2 - 1]["activation"] if i2 > 0 else self.input_activation
+        dz1 = b["dz"][i2 - 1][:rows] if i2 > 0 else (b["dx"][:rows] if need_input_grad else None)
+        k1, n2 = p2["weights"].shape
+        with self._span(f"tail fused {k1}->{n2}->{p3['weights'].shape[1]}"):
+            ops.tail2_train(b["a"][i2][:rows], p2["weights"], p2["biases"], p3["weights"], p3["biases"], labels,
+                            b["row_loss"][:rows], 1.0 / float(rows if denom is None else denom), act1,
+                            p2["activation"], self._ws if ws is None else ws, dz1=dz1)
+
+    def tail2_finish(self, lr: float, rows: Optional[int] = None, denom: Optional[int] = None,
+                     ws: Optional[torch.Tensor] = None) -> None:
+        """Second half on the current stream: loss reduction, both split-K reductions, SGD."""
+        rows = self._rows if rows is None else rows
+        b, lp = self._bufs, self.layer_params
+        p2, p3 = lp[-2], lp[-1]
+        ops.tail2_finish(rows, b["row_loss"][:rows], b["loss"], 1.0 / float(rows if denom is None else denom),
+                         self._ws if ws is None else ws, p2["weights"], p2["biases"], p3["weights"], p3["biases"], lr=lr)
 
     def gradients(self, rows: Optional[int] = None):
         """[(dW, db)] per local layer from the buffered activations/gradients (no update)."""

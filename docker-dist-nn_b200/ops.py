@@ -190,6 +190,42 @@ def output_layer_finish(rows: int, k: int, n: int, dtype: torch.dtype, row_loss:
                                            workspace.numel(), _stream(workspace)))
 
 
+def tail2_workspace_bytes(b: int, k1: int, n2: int, n3: int, dtype: torch.dtype) -> int:
+    """0 when the fused two-layer tail does not take this shape / dtype."""
+    return int(lib.ddnn_tail2_workspace_bytes(b, k1, n2, n3, _DT[dtype]))
+
+
+def tail2_train(a1: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor, w3: torch.Tensor, b3: torch.Tensor,
+                labels: torch.Tensor, row_loss: torch.Tensor, inv_denom: float, act1, act2,
+                workspace: torch.Tensor, dz1: Optional[torch.Tensor] = None) -> None:
+    """Fused last two layers (``ddnn_tail2_train``): row losses, dZ1 and the split partials in ``workspace``."""
+    _req(a1, torch.float32, "a1"); _req(w2, torch.float32, "w2"); _req(w3, torch.float32, "w3")
+    _req(b2, torch.float32, "b2"); _req(b3, torch.float32, "b3")
+    _req(labels, torch.int32, "labels"); _req(row_loss, torch.float32, "row_loss")
+    b, k1 = a1.shape
+    n2, n3 = w2.shape[1], w3.shape[1]
+    ids = [a if isinstance(a, int) else _lib.activation_id(a) for a in (act1, act2)]
+    with torch.cuda.device(a1.device):
+        check(lib.ddnn_tail2_train(_p(a1), _p(w2), _p(b2), _p(w3), _p(b3), _p(labels), _p(dz1), _p(row_loss), ids[0],
+                                   ids[1], b, k1, n2, n3, float(inv_denom), _DT[a1.dtype], _p(workspace),
+                                   workspace.numel(), _stream(a1)))
+
+
+def tail2_finish(rows: int, row_loss: torch.Tensor, loss: Optional[torch.Tensor], inv_denom: float,
+                 workspace: torch.Tensor, w2: torch.Tensor, b2: torch.Tensor, w3: torch.Tensor, b3: torch.Tensor,
+                 lr: float = 0.0, apply: bool = True, grads=None, accumulate_loss: bool = False) -> None:
+    """Second half on the CURRENT stream: loss + both reductions; SGD in place (``apply``) or the gradients into
+    ``grads = (dW2, db2, dW3, db3)``."""
+    k1, n2 = w2.shape
+    n3 = w3.shape[1]
+    g = grads if grads is not None else (None, None, None, None)
+    with torch.cuda.device(workspace.device):
+        check(lib.ddnn_tail2_finish(_p(row_loss), _p(loss), _p(w2), _p(b2), _p(w3), _p(b3), _p(g[0]), _p(g[1]),
+                                    _p(g[2]), _p(g[3]), float(lr), 1 if apply else 0, rows, k1, n2, n3,
+                                    float(inv_denom), 1 if accumulate_loss else 0, _DT[w2.dtype], _p(workspace),
+                                    workspace.numel(), _stream(workspace)))
+
+
 def _workspace(ws: Optional[torch.Tensor], b: int, k: int, n: int, like: torch.Tensor) -> torch.Tensor:
     need = dw_workspace_bytes(b, k, n, like.dtype)
     if ws is None or ws.numel() < need:

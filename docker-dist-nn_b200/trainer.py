@@ -48,6 +48,13 @@ class Trainer:
         L = self.layer
         L.begin_batch(x.shape[0])
         lr = self.lr if lr is None else lr
+        if L.can_fuse_tail2():
+            # small fp32 nets: the last two layers (forward, loss, backward, partial gradients) are one kernel
+            L.forward_train(x, 0, skip_last=2)
+            loss = L.tail2_step(labels, lr, x.shape[0], need_input_grad=False, side=self._side)
+            L.backward_and_step(lr, x.shape[0], side=self._side, top=len(L.layer_params) - 3)
+            torch.cuda.current_stream(self.device).wait_stream(self._side)
+            return loss
         if L.can_fuse_output_layer():
             # skinny output layer: logits, softmax-CE, dX, dW/db and the SGD update in one pass over its input
             L.forward_train(x, 0, skip_last=True)

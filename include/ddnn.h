@@ -174,6 +174,29 @@ int ddnn_output_layer_finish(const float* row_loss, float* loss,
                              void* workspace, size_t workspace_bytes, void* stream);
 size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype);
 
+/*
+ * Fused training step of the last TWO layers of a small fp32 MLP (hidden layer K1 -> N2 with activation act2,
+ * output layer N2 -> N3 with softmax-CE): K1 <= 128 and N2 <= 64 (both multiples of 4), N3 <= 16, fp32, A1 and
+ * dZ1 16-byte aligned; otherwise DDNN_ERR_UNSUPPORTED -- use the per-layer entry points.  One kernel reads
+ * A1[B,K1] (the output of the layer whose activation is act1) once and produces row_loss, dZ1 = gradient w.r.t.
+ * that layer's pre-activation (nullable) and the split partials of dW2, db2, dW3, db3 in `workspace`; A2, the
+ * logits and dZ2 / dZ3 never reach HBM.  ddnn_tail2_finish (any stream ordered after the first call, same
+ * workspace) reduces the loss and the partials and applies SGD (apply = 1: W2, b2, W3, b3 updated in place) or
+ * stores the four gradients (apply = 0).  Arithmetic, loss and update rule are those of ddnn_dense_forward /
+ * ddnn_softmax_ce / ddnn_dense_backward_* applied layer by layer.  No reference counterpart (grpc_node.py runs
+ * one process_matrix per layer and has no backward pass).
+ */
+size_t ddnn_tail2_workspace_bytes(int64_t B, int64_t K1, int64_t N2, int64_t N3, int dtype);
+int ddnn_tail2_train(const void* A1, const void* W2, const float* b2, const void* W3, const float* b3,
+                     const int32_t* labels, void* dZ1, float* row_loss, int act1, int act2,
+                     int64_t B, int64_t K1, int64_t N2, int64_t N3, float inv_denom, int dtype,
+                     void* workspace, size_t workspace_bytes, void* stream);
+int ddnn_tail2_finish(const float* row_loss, float* loss, float* W2, float* b2, float* W3, float* b3,
+                      float* dW2_out, float* db2_out, float* dW3_out, float* db3_out,
+                      float lr, int apply, int64_t B, int64_t K1, int64_t N2, int64_t N3,
+                      float inv_denom, int accumulate_loss, int dtype,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
 /* out[i] = bf16(in[i]) / fp32(in[i]) converters for staging host-provided fp32 data. */
 int ddnn_cast_f32_to_bf16(const float* in, void* out, int64_t n, void* stream);
 int ddnn_cast_bf16_to_f32(const void* in, float* out, int64_t n, void* stream);

@@ -331,3 +331,58 @@ def test_fused_output_layer_two_call_form(cuda_device, case):
     for x0, x1 in zip(*res):
         assert torch.equal(x0, x1)
     assert not torch.equal(res[0][0], to_dev(w0))  # the update happened
+
+
+@pytest.mark.parametrize("case", [(4096, 128, 64, 10, "relu", "relu"), (1000, 32, 16, 10, "relu", "sigmoid"),
+                                  (77, 100, 36, 3, "sigmoid", "linear"), (5000, 128, 64, 16, "linear", "relu"),
+                                  (33, 4, 4, 1, "relu", "relu"), (20000, 64, 48, 7, "relu", "sigmoid")])
+@pytest.mark.parametrize("mode", [0, 2])
+def test_fused_two_layer_tail(cuda_device, case, mode):
+    """ddnn_tail2_train / ddnn_tail2_finish (hidden layer + output layer, forward + softmax-CE + backward + SGD in
+    one kernel and its reducers) against the float64 oracle run layer by layer: loss, dZ1, the four gradients,
+    and the in-place update; FFMA variant (mode 0) and 3xTF32 mma.sync variant (default).  Shapes cover ragged
+    last tiles, more tiles than SMs (persistent loop), padded K1 / N2 / N3 and every activation pair."""
+    from ddnn_b200 import _lib, ops
+    _lib.set_f32_tensor_cores(mode)
+    try:
+        _tail2_case(ops, case)
+    finally:
+        _lib.set_f32_tensor_cores(None)
+
+
+def _tail2_case(ops, case):
+    b, k1, n2, n3, act1, act2 = case
+    rng = np.random.default_rng(40)
+    a1 = oracle.activate(rng.standard_normal((b, k1)), act1)
+    params = [{"weights": rng.standard_normal((k1, n2)) / np.sqrt(k1), "biases": rng.standard_normal(n2) * 0.1,
+               "activation": act2},
+              {"weights": rng.standard_normal((n2, n3)) / np.sqrt(n2), "biases": rng.standard_normal(n3) * 0.1,
+               "activation": "softmax"}]
+    y = rng.integers(0, n3, size=b)
+    acts, zs = oracle.forward_all(params, a1)
+    loss, dws, dbs, da1 = oracle.backward(params, acts, zs, y)
+    f1 = {"relu": (a1 > 0).astype(np.float64), "sigmoid": a1 * (1 - a1), "linear": np.ones_like(a1)}[act1]
+    ws = torch.empty(max(256, ops.tail2_workspace_bytes(b, k1, n2, n3, torch.float32)), dtype=torch.uint8, device="cuda")
+    assert ws.numel() > 256
+    a1d, yd = to_dev(a1), to_dev(y, torch.int32)
+    w2, b2, w3, b3 = (to_dev(params[0]["weights"]), to_dev(params[0]["biases"]), to_dev(params[1]["weights"]),
+                      to_dev(params[1]["biases"]))
+    row_loss, ls = torch.empty(b, device="cuda"), torch.zeros(1, device="cuda")
+    dz1 = torch.empty((b, k1), device="cuda")
+    ops.tail2_train(a1d, w2, b2, w3, b3, yd, row_loss, 1.0 / b, act1, act2, ws, dz1=dz1)
+    grads = (torch.empty((k1, n2), device="cuda"), torch.empty(n2, device="cuda"), torch.empty((n2, n3), device="cuda"),
+             torch.empty(n3, device="cuda"))
+    ops.tail2_finish(b, row_loss, ls, 1.0 / b, ws, w2, b2, w3, b3, apply=False, grads=grads)
+    assert abs(ls.item() - loss) < F32_TOL * abs(loss) + 1e-7
+    assert rel_err(to_np(dz1), da1 * f1) < F32_TOL
+    for got, ref in zip(grads, (dws[0], dbs[0], dws[1], dbs[1])):
+        assert rel_err(to_np(got), ref) < F32_TOL
+    # in-place SGD through the same partials
+    ops.tail2_finish(b, row_loss, None, 1.0 / b, ws, w2, b2, w3, b3, lr=0.2)
+    assert rel_err(to_np(w2), params[0]["weights"] - 0.2 * dws[0]) < F32_TOL
+    assert rel_err(to_np(b2), params[0]["biases"] - 0.2 * dbs[0]) < F32_TOL
+    assert rel_err(to_np(w3), params[1]["weights"] - 0.2 * dws[1]) < F32_TOL
+    assert rel_err(to_np(b3), params[1]["biases"] - 0.2 * dbs[1]) < F32_TOL
+    # shapes the kernel does not take: no workspace, DDNN_ERR_UNSUPPORTED
+    assert ops.tail2_workspace_bytes(b, 256, 64, 10, torch.float32) == 0
+    assert ops.tail2_workspace_bytes(b, 128, 64, 10, torch.bfloat16) == 0
