@@ -9,7 +9,8 @@ from ddnn_b200 import _lib, ops  # noqa: E402
 
 _lib.set_f32_tensor_cores(int(os.environ.get("MODE", "2")))
 dev = torch.device("cuda", 0)
-for (b, k, n) in [(4096, 784, 128), (4096, 128, 64), (16384, 784, 128), (4096, 2048, 512)]:
+shapes = [tuple(int(v) for v in a.split("x")) for a in sys.argv[1:]] or [(4096, 784, 128), (4096, 128, 64), (16384, 784, 128), (4096, 2048, 512)]
+for (b, k, n) in shapes:
     x = torch.rand((b, k), device=dev)
     w = torch.randn((k, n), device=dev) / k ** 0.5
     bias = torch.zeros(n, device=dev)
