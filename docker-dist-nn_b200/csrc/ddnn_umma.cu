@@ -199,7 +199,9 @@ __device__ __forceinline__ void epilogue_stage_bias(const UmmaParams& p, float* 
 
 template <int BN, int EPI>
 __device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, uint32_t tmem_acc, int row0, int n0,
-                                              int64_t zoff, int q, int lane) {
+                                              int64_t zoff, int q, int lane, int c0 = 0, int c1 = BN / 32) {
+  // chunks [c0, c1) of the tile's BN / 32 (an even count): with 8 epilogue warps two warps share a TMEM lane
+  // quarter and each takes half of the columns
   static_assert((BN / 32) % 2 == 0, "chunks are processed in pairs");
   const int nrows = min(32, p.M - row0);  // warp-uniform
   const int cg = lane & 3;
@@ -208,17 +210,17 @@ __device__ __forceinline__ void epilogue_tile(const UmmaParams& p, float* stg, u
   const float* bias_s = stg + 32 * Cfg<BN>::STG_PITCH;
   float va[32], vb[32];
   uint4 apa[4], apb[4];
-  tmem_ld32(tbase, va);
-  epilogue_load_aprev<BN, EPI>(p, apa, nrows, rbase + n0 + cg * 8, n0 + cg * 8, lane);
+  tmem_ld32(tbase + c0 * 32, va);
+  epilogue_load_aprev<BN, EPI>(p, apa, nrows, rbase + n0 + c0 * 32 + cg * 8, n0 + c0 * 32 + cg * 8, lane);
 #pragma unroll 1
-  for (int c = 0; c < BN / 32; c += 2) {
+  for (int c = c0; c < c1; c += 2) {
     int tcol = c * 32 + cg * 8, col = n0 + tcol;
     tmem_ld_wait();                        // chunk c has landed in va
     tmem_ld32(tbase + (c + 1) * 32, vb);   // chunk c+1 (accumulator and A_prev) streams in while chunk c is processed
     epilogue_load_aprev<BN, EPI>(p, apb, nrows, rbase + col + 32, col + 32, lane);
     epilogue_chunk<BN, EPI>(p, stg, bias_s, va, apa, nrows, rbase + col, col, tcol, lane);
     tmem_ld_wait();
-    if (c + 2 < BN / 32) {
+    if (c + 2 < c1) {
       tmem_ld32(tbase + (c + 2) * 32, va);
       epilogue_load_aprev<BN, EPI>(p, apa, nrows, rbase + col + 64, col + 64, lane);
     }
@@ -403,22 +405,30 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 // TMEM and runs its own epilogue.  Barriers: full[s] lives in CTA 0 and collects the TMA bytes of both
 // CTAs; tcgen05.commit multicasts the "stage free" and "accumulator ready" arrivals to both CTAs; CTA 1's
 // epilogue warps arrive remotely on CTA 0's "accumulator drained" barrier.
+// EW = number of epilogue warps.  4 for long reductions (the epilogue hides behind the MMAs); 8 for K <= 1024,
+// where a clock64 trace of the 65536 x 256 -> 256 layer showed the epilogue as the whole critical path (6 500
+// cycles per 128 x 256 tile against 2 000 of loads + MMAs, one warp per sub-partition issuing a dependent chain
+// at ~6 cycles per instruction): a second warp per TMEM lane quarter takes the other half of the columns.  Their
+// staging buffers cost one pipeline stage.
+template <int EW>
 struct Cfg2 {
   static constexpr int BN = 256;
-  static constexpr int STAGES = 6;
+  static constexpr int STAGES = EW == 8 ? 5 : 6;
+  static constexpr int THREADS = 128 + 32 * EW;
   static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;      // 128 rows of A per CTA
   static constexpr uint32_t B_BYTES = (BN / 2) * BLOCK_K * 2;     // 128 of the 256 B columns per CTA
   static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;      // 32 KB
   static constexpr uint32_t TMEM_COLS = 2 * BN;
   static constexpr uint32_t BAR_BYTES = (2 * STAGES + 4) * 8 + 16;
-  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + Cfg<256>::STG_BYTES;
+  static constexpr size_t SMEM_BYTES =
+      1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + (size_t)EW * Cfg<256>::STG_WARP * 4;
 };
 
-template <bool A_MN, bool B_MN, int EPI>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+template <bool A_MN, bool B_MN, int EPI, int EW>
+__global__ void __launch_bounds__(Cfg2<EW>::THREADS, 1)
 umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                       const UmmaParams p) {
-  using C = Cfg2;
+  using C = Cfg2<EW>;
   constexpr int BN = C::BN;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -449,7 +459,7 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);   // one multicast commit
-      mbar_init(tempty_bar(a), 8);  // used in CTA 0 only: 4 epilogue warps of each CTA
+      mbar_init(tempty_bar(a), 2 * EW);  // used in CTA 0 only: the epilogue warps of both CTAs
     }
     fence_barrier_init();
   }
@@ -529,8 +539,9 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     __syncwarp();
   } else if (warp >= 4) {
     // ===================== epilogue (both CTAs, own 128 rows) =====================
-    const int q = warp & 3;
-    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * Cfg<256>::STG_WARP;
+    const int q = warp & 3, ew = warp - 4;  // TMEM lane quarter; index of this epilogue warp
+    const int c0 = EW == 8 ? (ew >> 2) * (BN / 64) : 0, c1 = EW == 8 ? c0 + BN / 64 : BN / 32;
+    float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + ew * Cfg<256>::STG_WARP;
     uint32_t as = 0, aphase = 0;
     for (int tile = pair; tile < total_tiles; tile += num_pairs) {
       const TileCoord t = decode_tile(tile, p);
@@ -538,7 +549,7 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       epilogue_tile<BN, EPI>(p, stg, tmem_base + as * BN, t.m_blk * 256 + (int)rank * BLOCK_M + q * 32, t.n_blk * BN,
-                             EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0, q, lane);
+                             EPI == EPI_STORE ? (int64_t)t.ks * p.zrows : 0, q, lane, c0, c1);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_remote(tempty_bar(as), 0);
@@ -670,10 +681,10 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p
 
 std::atomic<int> g_use_pair{1};  // 1: CTA-pair (cta_group::2) kernel for large BN = 256 problems
 
-template <bool A_MN, bool B_MN, int EPI>
-int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cudaStream_t st) {
-  auto kern = umma_pair_gemm_kernel<A_MN, B_MN, EPI>;
-  if (int rc = ensure_dynamic_smem((const void*)kern, Cfg2::SMEM_BYTES)) return rc;
+template <bool A_MN, bool B_MN, int EPI, int EW>
+int launch_pair_ew(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cudaStream_t st) {
+  auto kern = umma_pair_gemm_kernel<A_MN, B_MN, EPI, EW>;
+  if (int rc = ensure_dynamic_smem((const void*)kern, Cfg2<EW>::SMEM_BYTES)) return rc;
   // L2 eviction-priority policy of the operand loads (createpolicy encodings: normal 0x10.., evict_first
   // 0x12F0.., evict_last 0x14F0..).  Measured on 8192^3 (ncu, dram__bytes_read per launch): normal 1.09 GB,
   // A = evict_last 1.07 GB (no gain: the A row-blocks of a rasterisation group are not what gets evicted),
@@ -691,8 +702,8 @@ int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cuda
   if (pairs > total) pairs = total;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(2 * pairs);
-  cfg.blockDim = dim3(NUM_THREADS);
-  cfg.dynamicSmemBytes = Cfg2::SMEM_BYTES;
+  cfg.blockDim = dim3(Cfg2<EW>::THREADS);
+  cfg.dynamicSmemBytes = Cfg2<EW>::SMEM_BYTES;
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -706,6 +717,13 @@ int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cuda
   DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
   count_launch();
   return DDNN_OK;
+}
+
+template <bool A_MN, bool B_MN, int EPI>
+int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p, cudaStream_t st) {
+  // short reductions are epilogue-bound: 8 epilogue warps (and one stage less); long ones are MMA-bound
+  if (p.num_kb <= 16) return launch_pair_ew<A_MN, B_MN, EPI, 8>(ta, tb, p, st);
+  return launch_pair_ew<A_MN, B_MN, EPI, 4>(ta, tb, p, st);
 }
 
 // the pair kernel pays off when there are at least two waves of 256x256 tiles and no split-K
