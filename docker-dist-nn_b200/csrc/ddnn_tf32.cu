@@ -2,16 +2,17 @@
 // tcgen05.mma.kind::tf32 with fp32 accumulators in TMEM.
 //
 // The fp32 path of the reference-parity contract (1e-5 relative) cannot use bf16, and FFMA tops out near
-// 20 TFLOP/s on the MNIST layers.  Every fp32 operand x is split as x = hi + lo with hi = rna_tf32(x) and
-// lo = x - hi (exact in fp32, |lo| <= 2^-11 |x|), and the product is evaluated as
-//     A.B  ~=  A_hi.B_hi  +  (A_lo.B_hi + A_hi.B_lo)            (dropped: A_lo.B_lo ~ 2^-22)
+// 20 TFLOP/s on the MNIST layers.  Every fp32 operand x is split as x = hi + lo with hi = trunc_tf32(x) (what
+// the tensor core reads from a raw fp32 word) and lo = x - hi (exact in fp32, |lo| < 2^-10 |x|), and the
+// product is evaluated as
+//     A.B  ~=  A_hi.B_hi  +  (A_lo.B_hi + A_hi.B_lo)            (dropped: A_lo.B_lo ~ 2^-20)
 // with the bracketed correction in its OWN TMEM accumulator, added in the epilogue -- the small terms are not
 // rounded against the large running sum.
 //
-// Pipeline per CTA (persistent, one per SM, 384 threads):
+// Pipeline per CTA (persistent, one per SM, 512 threads):
 //   warp 0      TMA producer: raw fp32 A / B tiles (128-byte swizzle, 32 fp32 per row) into the `hi` slots
-//   warps 8-15  converters: rewrite each 16-byte chunk of the stage in place as hi and store lo in the sibling
-//               slot.  The split is elementwise, so it is done on the raw swizzled bytes: no layout math.
+//   warps 8-15  converters: read each 16-byte chunk of the stage and store its lo part at the same offset of a
+//               lo slot.  The split is elementwise, so it is done on the raw swizzled bytes: no layout math.
 //   warp 1      MMA issuer: 3 x (BLOCK_K / 8) tcgen05.mma per stage
 //   warp 2      TMEM allocator; warps 4-7 epilogue (TMEM -> 32x32 transpose -> fused functor -> 16-byte stores)
 // Same three operand layouts as the bf16 family (descriptor major-ness instead of transposes in memory).
@@ -48,11 +49,10 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
       : "memory");
 }
 
-// round-to-nearest (ties away) to the 10-bit tf32 mantissa on the bit pattern: what cvt.rna.tf32.f32 does for
-// finite inputs, without its Inf/NaN special-casing (4 instructions per element in SASS instead of 2)
-__device__ __forceinline__ float rna_tf32(float x) {
-  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
-}
+// kind::tf32 reads the top 19 bits of each fp32 operand word (the low 13 mantissa bits are ignored: measured -- with
+// raw fp32 words as the `hi` operand and lo = x - trunc(x) the results stay at the 1e-6 level, a rounding unit
+// would have shown 2^-11).  So the raw tile IS the hi operand and only lo has to be written.
+__device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
 
 // K-major tile [rows][32 fp32] (row = 128 B, 8-row swizzle atoms 1024 B apart): step k (8 elements) by 32 bytes.
 // MN-major tile: 32-bit MN-major operands exist only in the SWIZZLE_128B_BASE32B layout (32-byte swizzle units,
@@ -263,7 +263,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     }
     __syncwarp();
   } else if (warp >= 8) {
-    // ===================== converters: x -> (hi = rna_tf32(x), lo = x - hi) on the raw stage bytes =====================
+    // ===================== converters: lo = x - trunc_tf32(x) from the raw stage bytes =====================
     const int ct = threadIdx.x - 256;  // 0..CONV_THREADS-1
     constexpr int A_CH = C::A_BYTES / 16, B_CH = C::B_BYTES / 16;
     constexpr int PER = (A_CH + B_CH + CONV_THREADS - 1) / CONV_THREADS;
@@ -290,12 +290,10 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           const int i = ct + j * CONV_THREADS;
           const bool is_a = j * CONV_THREADS < A_CH;
           if (is_a || i < A_CH + B_CH) {
-            uint8_t* ph = base + i * 16;
             float4 h, l;
-            h.x = rna_tf32(x[j].x); h.y = rna_tf32(x[j].y); h.z = rna_tf32(x[j].z); h.w = rna_tf32(x[j].w);
+            h.x = trunc_tf32(x[j].x); h.y = trunc_tf32(x[j].y); h.z = trunc_tf32(x[j].z); h.w = trunc_tf32(x[j].w);
             l.x = x[j].x - h.x; l.y = x[j].y - h.y; l.z = x[j].z - h.z; l.w = x[j].w - h.w;
-            *reinterpret_cast<float4*>(ph) = h;
-            *reinterpret_cast<float4*>(lobase + i * 16) = l;
+            *reinterpret_cast<float4*>(lobase + i * 16) = l;  // the raw tile stays in place as the hi operand
           }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to tcgen05.mma
