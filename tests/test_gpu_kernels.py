@@ -214,7 +214,7 @@ def test_skinny_output_layer_kernels(cuda_device, bkn, dt):
 
 @pytest.mark.parametrize("shape", [(4096, 784, 128), (333, 128, 64), (4096, 64, 128), (1000, 100, 132),
                                    (2048, 2048, 256), (777, 36, 32), (5000, 260, 68), (20000, 64, 4096),
-                                   (256, 4096, 64)])
+                                   (256, 4096, 64), (1, 784, 128), (5, 64, 32)])
 @pytest.mark.parametrize("mode", [0, 1, 2])
 def test_f32_inner_product_cores(cuda_device, shape, mode):
     """fp32 forward, dX and dW on 16-byte-aligned shapes with each inner product: FFMA (0), error-compensated

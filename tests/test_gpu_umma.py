@@ -17,7 +17,7 @@ ACC_TOL = 1e-4        # fp32 accumulation vs float64 on identical operands
 BF16_OUT_TOL = 6e-3   # + one round-to-bf16 of the result (2^-8 relative, normalised)
 
 # (B, K, N): one tile, many tiles, ragged M/N/K tails, narrow, K not a multiple of 64
-SHAPES = [(128, 64, 64), (128, 256, 256), (256, 512, 128), (300, 200, 72), (1024, 784, 256), (96, 1024, 520),
+SHAPES = [(128, 64, 64), (128, 256, 256), (256, 512, 128), (300, 200, 72), (1024, 784, 256), (96, 1024, 520), (3, 128, 64),
           (2048, 2048, 2048)]
 
 
