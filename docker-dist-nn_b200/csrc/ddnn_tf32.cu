@@ -77,16 +77,19 @@ struct TCfg {
   // Two rings.  The deep one receives the raw TMA tiles (rewritten in place as `hi`): these GEMMs are small and
   // latency-bound, so what matters is bytes in flight per SM.  The `lo` halves only live from the conversion of
   // a k-block to the retirement of its MMAs: two slots.
-  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;  // [A raw -> hi][B raw -> hi]
-  static constexpr int STAGES = BN == 128 ? 4 : (BN == 64 ? 6 : 7);
-  static constexpr int LO_SLOTS = 2;                          // [A lo][B lo] each
+  // stage = [A raw = A hi][B raw = B hi][B lo]: B hi and B lo are adjacent so that ONE MMA with N = 2 BN computes
+  // A_hi.[B_hi | B_lo] into the adjacent main | correction accumulator columns (8 instead of 12 MMAs per k-block,
+  // a third fewer A reads from shared memory).  A lo lives in the 2-slot side ring.
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + 2 * B_BYTES;
+  static constexpr int STAGES = BN == 128 ? 3 : (BN == 64 ? 5 : 7);
+  static constexpr int LO_SLOTS = 2;                          // [A lo] each
   static constexpr uint32_t TMEM_COLS = 4 * BN < 32 ? 32 : 4 * BN;  // 2 stages x (main, correction)
   static constexpr uint32_t STG_PITCH = 36;
   static constexpr uint32_t STG_BYTES = 4 * 32 * STG_PITCH * 4;
   static constexpr uint32_t BAR_BYTES = ((3 * STAGES + LO_SLOTS + 4) * 8 + 16 + 15) / 16 * 16;  // keeps stg 16-B aligned
   static constexpr uint32_t ONES_BYTES = 1024;  // all-ones fp32 A operand of the fused bias-gradient MMA (one k-step)
   static constexpr size_t SMEM_BYTES =
-      1024 + (size_t)(STAGES + LO_SLOTS) * STAGE_BYTES + BAR_BYTES + STG_BYTES + 128 + ONES_BYTES;
+      1024 + (size_t)STAGES * STAGE_BYTES + (size_t)LO_SLOTS * A_BYTES + BAR_BYTES + STG_BYTES + 128 + ONES_BYTES;
 };
 
 // Epilogue of one 128 x BN tile for the warp owning TMEM lanes [32q, 32q+32): main + correction accumulators,
@@ -133,7 +136,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
   const uint32_t lo_ring = tiles + C::STAGES * C::STAGE_BYTES;
-  const uint32_t bars = lo_ring + C::LO_SLOTS * C::STAGE_BYTES;
+  const uint32_t bars = lo_ring + C::LO_SLOTS * C::A_BYTES;
   auto full_bar = [&](int s) { return bars + 8u * s; };                      // TMA bytes landed
   auto conv_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };        // hi / lo written (all converter warps)
   auto empty_bar = [&](int s) { return bars + 8u * (2 * C::STAGES + s); };   // MMAs of the stage retired
@@ -218,12 +221,11 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
-      constexpr uint32_t idesc = tf32_idesc<A_MN, B_MN, BN>();
+      constexpr uint32_t idesc = tf32_idesc<A_MN, B_MN, BN>(), idesc2 = tf32_idesc<A_MN, B_MN, 2 * BN>();
       constexpr uint32_t A_STEP = A_MN ? UMMA_K * 128 : UMMA_K * 4, B_STEP = B_MN ? UMMA_K * 128 : UMMA_K * 4;
       const uint64_t desc_a = tf32_desc<A_MN>(tiles, 0);                    // A hi slot of stage 0, k-step 0
       const uint64_t desc_b = tf32_desc<B_MN>(tiles + C::A_BYTES, 0);       // B hi slot of stage 0
       const uint64_t desc_al = tf32_desc<A_MN>(lo_ring, 0);                 // A lo of slot 0
-      const uint64_t desc_bl = tf32_desc<B_MN>(lo_ring + C::A_BYTES, 0);
       const uint64_t ones_desc = make_desc_layout(ones_base, 0, 512, 1u);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0, u = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
@@ -235,21 +237,17 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           mbar_wait(conv_bar(stage), phase);  // hi / lo of this stage are in place
           tc_fence_after();
           // all descriptors of the ring differ only in the 16-byte-granular start-address field
-          const uint64_t so = (uint64_t)((stage * C::STAGE_BYTES) >> 4), lo = (uint64_t)((u * C::STAGE_BYTES) >> 4);
+          const uint64_t so = (uint64_t)((stage * C::STAGE_BYTES) >> 4), lo = (uint64_t)((u * C::A_BYTES) >> 4);
           const uint64_t ah = desc_a + so, al = desc_al + lo;
-          const uint64_t bh = desc_b + so, bl = desc_bl + lo;
+          const uint64_t bh = desc_b + so;  // B hi; B lo follows it: N = 2 BN covers both
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
             const uint32_t acc = (kb > t.kb0 || k > 0) ? 1u : 0u;
             const uint64_t ka = (uint64_t)k * (A_STEP >> 4), kbo = (uint64_t)k * (B_STEP >> 4);
-            umma_tf32(d_corr, al + ka, bh + kbo, idesc, acc);
-            umma_tf32(d_corr, ah + ka, bl + kbo, idesc, 1u);
-            umma_tf32(d_main, ah + ka, bh + kbo, idesc, acc);
-            if (fuse_db && t.m_blk == 0) {
-              // bias gradient: (ones . dZ_hi) and (ones . dZ_lo) into the idle second accumulator stage
-              umma_tf32(tmem_base + 2 * BN, ones_desc, bh + kbo, idesc, acc);
-              umma_tf32(tmem_base + 3 * BN, ones_desc, bl + kbo, idesc, acc);
-            }
+            umma_tf32(d_main, ah + ka, bh + kbo, idesc2, acc);  // main | corr (+)= A_hi . [B_hi | B_lo]
+            umma_tf32(d_corr, al + ka, bh + kbo, idesc, 1u);    // corr += A_lo . B_hi
+            if (fuse_db && t.m_blk == 0)  // bias gradient: ones . [dZ_hi | dZ_lo] into the idle second accumulator stage
+              umma_tf32(tmem_base + 2 * BN, ones_desc, bh + kbo, idesc2, acc);
           }
           umma_commit(empty_bar(stage));
           umma_commit(lofree_bar(u));
@@ -275,7 +273,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         mbar_wait(full_bar(stage), phase);
         mbar_wait(lofree_bar(u), uphase ^ 1);  // the MMAs of the k-block that last used this lo slot have retired
         uint8_t* base = smem_raw + (tiles + stage * C::STAGE_BYTES - raw);
-        uint8_t* lobase = smem_raw + (lo_ring + u * C::STAGE_BYTES - raw);
+        uint8_t* alo = smem_raw + (lo_ring + u * C::A_BYTES - raw);  // A lo slot; B lo sits behind B raw in the stage
         float4 x[PER];
         // all loads first (PER independent 16-byte loads in flight), then the split, then the stores
 #pragma unroll
@@ -293,7 +291,8 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
             float4 h, l;
             h.x = trunc_tf32(x[j].x); h.y = trunc_tf32(x[j].y); h.z = trunc_tf32(x[j].z); h.w = trunc_tf32(x[j].w);
             l.x = x[j].x - h.x; l.y = x[j].y - h.y; l.z = x[j].z - h.z; l.w = x[j].w - h.w;
-            *reinterpret_cast<float4*>(lobase + i * 16) = l;  // the raw tile stays in place as the hi operand
+            // the raw tile stays in place as the hi operand
+            *reinterpret_cast<float4*>(is_a ? alo + i * 16 : base + C::B_BYTES + i * 16) = l;
           }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to tcgen05.mma
