@@ -163,6 +163,34 @@ def test_cuda_graph_step_equals_eager(cuda_device):
     assert np.isfinite(l)
 
 
+@pytest.mark.parametrize("dtype,dims", [("f32", [784, 128, 64, 10]), ("bf16", [784, 256, 256, 10]),
+                                        ("f32", [100, 200, 150, 12])])
+def test_programmatic_dependent_launch_is_transparent(cuda_device, dtype, dims):
+    """ddnn_set_pdl(0 / 1): chaining the kernels of a step with programmatic dependent launch (every kernel waits
+    for its predecessor before touching global memory) must not change a single bit of losses or weights, eagerly
+    and in a captured graph."""
+    from ddnn_b200 import Trainer, _lib
+    acts = ["relu", "relu", "softmax"]
+    x, y = synthetic_batch(512, dims[0], dims[-1], seed=5)
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    results = []
+    try:
+        for pdl in (False, True):
+            _lib.set_pdl(pdl)
+            t = Trainer(make_params(dims, acts, seed=2), dtype=dtype)
+            losses = [t.train_step(xd, yd, 0.05).item() for _ in range(3)]
+            t.capture(512, lr=0.05)
+            sx, sy = t.static_inputs
+            sx.copy_(xd); sy.copy_(yd)
+            losses += [t.replay().item() for _ in range(3)]
+            results.append((losses, t.export_params()))
+    finally:
+        _lib.set_pdl(True)
+    assert results[0][0] == results[1][0]
+    for a, b in zip(results[0][1], results[1][1]):
+        assert np.array_equal(a["weights"], b["weights"]) and np.array_equal(a["biases"], b["biases"])
+
+
 def test_bf16_training_tracks_loss_curve(cuda_device):
     """bf16 tensor-core path: looser bound, matching loss curve (north_star)."""
     from ddnn_b200 import Trainer
