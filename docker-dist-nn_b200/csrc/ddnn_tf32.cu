@@ -11,9 +11,10 @@
 //
 // Pipeline per CTA (persistent, one per SM, 512 threads):
 //   warp 0      TMA producer: raw fp32 A / B tiles (128-byte swizzle, 32 fp32 per row) into the `hi` slots
-//   warps 8-15  converters: read each 16-byte chunk of the stage and store its lo part at the same offset of a
-//               lo slot.  The split is elementwise, so it is done on the raw swizzled bytes: no layout math.
-//   warp 1      MMA issuer: 3 x (BLOCK_K / 8) tcgen05.mma per stage
+//   warps 8-15  converters: read each 16-byte chunk of the stage and store its lo part (A: same offset of a lo
+//               slot; B: behind B hi in the stage).  The split is elementwise, so it is done on the raw swizzled
+//               bytes: no layout math.
+//   warp 1      MMA issuer: 2 x (BLOCK_K / 8) tcgen05.mma per stage (A_hi.[B_hi | B_lo] with N = 2 BN, A_lo.B_hi)
 //   warp 2      TMEM allocator; warps 4-7 epilogue (TMEM -> 32x32 transpose -> fused functor -> 16-byte stores)
 // Same three operand layouts as the bf16 family (descriptor major-ness instead of transposes in memory).
 #include <cuda.h>
@@ -74,12 +75,10 @@ template <int BN>
 struct TCfg {
   static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 4;  // 16 KB (one of hi / lo)
   static constexpr uint32_t B_BYTES = BN * BLOCK_K * 4;
-  // Two rings.  The deep one receives the raw TMA tiles (rewritten in place as `hi`): these GEMMs are small and
-  // latency-bound, so what matters is bytes in flight per SM.  The `lo` halves only live from the conversion of
-  // a k-block to the retirement of its MMAs: two slots.
-  // stage = [A raw = A hi][B raw = B hi][B lo]: B hi and B lo are adjacent so that ONE MMA with N = 2 BN computes
-  // A_hi.[B_hi | B_lo] into the adjacent main | correction accumulator columns (8 instead of 12 MMAs per k-block,
-  // a third fewer A reads from shared memory).  A lo lives in the 2-slot side ring.
+  // A ring of stages [A raw = A hi][B raw = B hi][B lo] and a 2-slot side ring for A lo.  The raw TMA tiles are the
+  // hi operands as they are.  B hi and B lo are adjacent so that ONE MMA with N = 2 BN computes A_hi.[B_hi | B_lo]
+  // into the adjacent main | correction accumulator columns (8 instead of 12 MMAs per k-block, a third fewer A
+  // reads from shared memory).  An A lo slot lives from the conversion of a k-block to the retirement of its MMAs.
   static constexpr uint32_t STAGE_BYTES = A_BYTES + 2 * B_BYTES;
   static constexpr int STAGES = BN == 128 ? 3 : (BN == 64 ? 5 : 7);
   static constexpr int LO_SLOTS = 2;                          // [A lo] each
