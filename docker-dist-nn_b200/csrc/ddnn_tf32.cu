@@ -54,6 +54,9 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
 // raw fp32 words as the `hi` operand and lo = x - trunc(x) the results stay at the 1e-6 level, a rounding unit
 // would have shown 2^-11).  So the raw tile IS the hi operand and only lo has to be written.
 __device__ __forceinline__ float trunc_tf32(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+__device__ __forceinline__ float rn_tf32(float x) {  // nearest (ties away) on the bit pattern, finite inputs
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
 
 // K-major tile [rows][32 fp32] (row = 128 B, 8-row swizzle atoms 1024 B apart): step k (8 elements) by 32 bytes.
 // MN-major tile: 32-bit MN-major operands exist only in the SWIZZLE_128B_BASE32B layout (32-byte swizzle units,
@@ -82,7 +85,14 @@ struct TCfg {
   static constexpr uint32_t STAGE_BYTES = A_BYTES + 2 * B_BYTES;
   static constexpr int STAGES = BN == 128 ? 3 : (BN == 64 ? 5 : 7);
   static constexpr int LO_SLOTS = 2;                          // [A lo] each
-  static constexpr uint32_t TMEM_COLS = 4 * BN < 32 ? 32 : 4 * BN;  // 2 stages x (main, correction)
+  // The tensor core adds into its fp32 accumulator with truncation: a BIASED error that grows with the number of
+  // accumulation steps and survives in sums whose terms cancel (bias gradients came out 1e-5 off on the 4096-row
+  // MNIST step, against 3e-6 with FFMA).  Forward / dX tiles therefore rotate their k-blocks over NACC
+  // (main | correction) accumulator sets, summed in fp32 by the epilogue: chains 1 / NACC as long.  512 columns
+  // = 2 tile stages x NACC sets x 2 BN for every BN.  dW tiles are split-K (short chains) and use one set; their
+  // second stage holds the bias-gradient accumulators.
+  static constexpr int NACC_FWD = BN == 32 ? 4 : (BN == 64 ? 2 : 1);
+  static constexpr uint32_t TMEM_COLS = 512;
   static constexpr uint32_t STG_PITCH = 36;
   static constexpr uint32_t STG_BYTES = 4 * 32 * STG_PITCH * 4;
   static constexpr uint32_t BAR_BYTES = ((3 * STAGES + LO_SLOTS + 4) * 8 + 16 + 15) / 16 * 16;  // keeps stg 16-B aligned
@@ -96,7 +106,8 @@ struct TCfg {
 // with two 4-column groups per row (N % 4 == 0: a group is all in or all out).
 template <int BN, typename Epi>
 __device__ __forceinline__ void tf32_epilogue(const Epi& epi, int M, int N, float* stg, uint32_t tmem_main,
-                                              uint32_t tmem_corr, int row0, int n0, int64_t zoff, int q, int lane) {
+                                              uint32_t tmem_corr, int nsets, int row0, int n0, int64_t zoff, int q,
+                                              int lane) {
   const int nrows = min(32, M - row0);  // warp-uniform
   const int cg = lane & 3, r8 = lane >> 2;
   const uint32_t lane_off = (uint32_t)(q * 32) << 16;
@@ -107,10 +118,19 @@ __device__ __forceinline__ void tf32_epilogue(const Epi& epi, int M, int N, floa
     tmem_ld32(tmem_corr + c * 32 + lane_off, w);
     tmem_ld_wait();
 #pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] += w[j];
+    for (int sset = 1; sset < nsets; ++sset) {  // the other accumulator sets of this tile (2 BN columns apart)
+      float u[32];
+      tmem_ld32(tmem_main + sset * 2 * BN + c * 32 + lane_off, u);
+      tmem_ld32(tmem_corr + sset * 2 * BN + c * 32 + lane_off, w);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] += u[j] + w[j];
+    }
+#pragma unroll
     for (int j = 0; j < 8; ++j)
       *reinterpret_cast<float4*>(&stg[lane * TCfg<BN>::STG_PITCH + 4 * j]) =
-          make_float4(v[4 * j] + w[4 * j], v[4 * j + 1] + w[4 * j + 1], v[4 * j + 2] + w[4 * j + 2],
-                      v[4 * j + 3] + w[4 * j + 3]);
+          make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
     __syncwarp();
     const int col = n0 + c * 32 + cg * 8;
 #pragma unroll
@@ -131,6 +151,7 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const Tf32Params p, const Epi epi) {
   using C = TCfg<BN>;
+  constexpr int NACC = (A_MN && B_MN) ? 1 : C::NACC_FWD;  // accumulator sets per tile (see TCfg)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
@@ -231,7 +252,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
         const TileCoord t = decode_tile(tile, p);
         mbar_wait(tempty_bar(as), aphase ^ 1);
         tc_fence_after();
-        const uint32_t d_main = tmem_base + as * (2 * BN), d_corr = d_main + BN;
+        const uint32_t d_stage = tmem_base + as * (NACC * 2 * BN);
         for (int kb = t.kb0; kb < t.kb1; ++kb) {
           mbar_wait(conv_bar(stage), phase);  // hi / lo of this stage are in place
           tc_fence_after();
@@ -239,14 +260,16 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           const uint64_t so = (uint64_t)((stage * C::STAGE_BYTES) >> 4), lo = (uint64_t)((u * C::A_BYTES) >> 4);
           const uint64_t ah = desc_a + so, al = desc_al + lo;
           const uint64_t bh = desc_b + so;  // B hi; B lo follows it: N = 2 BN covers both
+          const int kj = kb - t.kb0;
+          const uint32_t d_main = d_stage + (uint32_t)(kj % NACC) * (2 * BN), d_corr = d_main + BN;
 #pragma unroll
           for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-            const uint32_t acc = (kb > t.kb0 || k > 0) ? 1u : 0u;
+            const uint32_t acc = (kj >= NACC || k > 0) ? 1u : 0u;  // the first k-block of each set overwrites
             const uint64_t ka = (uint64_t)k * (A_STEP >> 4), kbo = (uint64_t)k * (B_STEP >> 4);
             umma_tf32(d_main, ah + ka, bh + kbo, idesc2, acc);  // main | corr (+)= A_hi . [B_hi | B_lo]
             umma_tf32(d_corr, al + ka, bh + kbo, idesc, 1u);    // corr += A_lo . B_hi
             if (fuse_db && t.m_blk == 0)  // bias gradient: ones . [dZ_hi | dZ_lo] into the idle second accumulator stage
-              umma_tf32(tmem_base + 2 * BN, ones_desc, bh + kbo, idesc2, acc);
+              umma_tf32(tmem_base + 2 * BN, ones_desc, bh + kbo, idesc2, (kj > 0 || k > 0) ? 1u : 0u);
           }
           umma_commit(empty_bar(stage));
           umma_commit(lofree_bar(u));
@@ -289,7 +312,10 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           if (is_a || i < A_CH + B_CH) {
             float4 h, l;
             h.x = trunc_tf32(x[j].x); h.y = trunc_tf32(x[j].y); h.z = trunc_tf32(x[j].z); h.w = trunc_tf32(x[j].w);
-            l.x = x[j].x - h.x; l.y = x[j].y - h.y; l.z = x[j].z - h.z; l.w = x[j].w - h.w;
+            // lo has up to 13 significant bits and the tensor core will truncate it to 10: round it here (to
+            // nearest), otherwise every lo is cut towards zero -- a bias that survives in sums whose terms
+            // cancel (bias gradients: 1e-5 on the 4096-row MNIST step)
+            l.x = rn_tf32(x[j].x - h.x); l.y = rn_tf32(x[j].y - h.y); l.z = rn_tf32(x[j].z - h.z); l.w = rn_tf32(x[j].w - h.w);
             // the raw tile stays in place as the hi operand
             *reinterpret_cast<float4*>(is_a ? alo + i * 16 : base + C::B_BYTES + i * 16) = l;
           }
@@ -311,8 +337,9 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const TileCoord t = decode_tile(tile, p);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
-      const uint32_t d_main = tmem_base + as * (2 * BN);
-      tf32_epilogue<BN, Epi>(epi, p.M, p.N, stg, d_main, d_main + BN, t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
+      const uint32_t d_main = tmem_base + as * (NACC * 2 * BN);
+      tf32_epilogue<BN, Epi>(epi, p.M, p.N, stg, d_main, d_main + BN, min(NACC, t.kb1 - t.kb0),
+                             t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
                              (int64_t)t.ks * p.zrows, q, lane);
       if (fuse_db && t.m_blk == 0 && q == 0) {
         // every row of the ones-accumulators holds the column sums; TMEM lane 0 belongs to lane 0 of this warp

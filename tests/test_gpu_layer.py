@@ -325,3 +325,52 @@ def test_json_export_roundtrip_and_eval_driver(cuda_device, tmp_path):
     assert n1 == 100 and len(pb1) == 1 and c1 == int(ref_out[7].argmax() == y[7])
     assert infer.main(["--config", str(path), "--inputs", str(inputs), "--batch-size", "40"]) == 0
     assert infer.main(["200", "--config", str(path), "--inputs", str(inputs)]) == 1  # index out of range
+
+
+def test_default_bench_configuration_matches_oracle(cuda_device):
+    """BASELINE.json configs[1] at its own size: 784-128-64-10, batch 4096, fp32, the captured 7-launch step of
+    bench.py (tcgen05 3xTF32 forward / dW, fused two-layer tail, side-stream reducers): 3 steps against the float64
+    oracle, losses and every weight within the fp32 bound."""
+    from ddnn_b200 import Trainer
+    dims, acts = [784, 128, 64, 10], ["relu", "relu", "softmax"]
+    ref = [dict(p) for p in make_params(dims, acts, seed=1)]
+    x, y = synthetic_batch(4096, 784, 10, seed=0)
+    t = Trainer(make_params(dims, acts, seed=1))
+    assert t.layer.begin_batch(4096) is None and t.layer.can_fuse_tail2()
+    t.capture(4096, lr=0.01)
+    sx, sy = t.static_inputs
+    sx.copy_(to_dev(x)); sy.copy_(to_dev(y, torch.int32))
+    for _ in range(3):
+        got = t.replay().item()
+        want = oracle.train_step(ref, x, y, 0.01)
+        assert abs(got - want) < F32_TOL * want
+    for g, r in zip(t.export_params(), ref):
+        assert rel_err(g["weights"], r["weights"]) < F32_TOL
+        # Biases are 0.01 +- 1e-4, so 1e-5 of max|b| is 1e-7 absolute = a fraction of ONE dZ element times lr: a single
+        # ReLU gate that flips because a pre-activation is closer to zero than the fp32 forward error (786 432 gates
+        # per step here) moves a bias by that much -- in any fp32 implementation (measured: the same 1.0e-5 / 2.9e-5
+        # with mma.sync and tcgen05 products and with either tail kernel, whatever their forward accuracy).
+        assert rel_err(g["biases"], r["biases"]) < 5 * F32_TOL
+
+
+def test_narrow_configuration_tracks_oracle_at_full_size(cuda_device):
+    """BASELINE.json configs[4] at its own size: 784-256-256-10, batch 65536, bf16 (pair-kernel GEMMs with 8
+    epilogue warps, split-K dW with the ones-MMA bias gradient, output layer on mma.sync): two steps against the
+    float64 oracle within the bf16 bounds; the bias gradients (the fused paths) within the gradient bound."""
+    from ddnn_b200 import Trainer
+    dims, acts = [784, 256, 256, 10], ["relu", "relu", "softmax"]
+    ref = [dict(p) for p in make_params(dims, acts, seed=1)]
+    before = [dict(p) for p in make_params(dims, acts, seed=1)]
+    x, y = synthetic_batch(65536, 784, 10, seed=0)
+    t = Trainer(make_params(dims, acts, seed=1), dtype="bf16")
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    lr = 0.5  # large enough for the update to stand out of the bf16 noise
+    for _ in range(2):
+        got = t.train_step(xd, yd, lr).item()
+        want = oracle.train_step(ref, x, y, lr)
+        assert abs(got - want) < 2e-2 * want
+    for g, r, b0 in zip(t.export_params(), ref, before):
+        assert rel_err(g["weights"], r["weights"]) < BF16_ACT_TOL
+        # the UPDATE itself (difference to the initial weights), not just the weights it barely moves
+        assert rel_err(g["weights"] - b0["weights"], r["weights"] - b0["weights"]) < 0.1
+        assert rel_err(g["biases"] - b0["biases"], r["biases"] - b0["biases"]) < 0.1
