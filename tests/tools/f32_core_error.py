@@ -6,7 +6,7 @@ import sys
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import oracle  # noqa: E402
 from ddnn_b200 import Trainer, _lib, ops  # noqa: E402
 from ddnn_b200.config import make_params, synthetic_batch  # noqa: E402
