@@ -66,10 +66,11 @@ static bool use_umma(int dtype, int64_t B, int64_t K, int64_t N, std::initialize
 // fp32 operands on tcgen05 (error-compensated TF32): 16-byte aligned rows and pointers, widths >= 32.
 // `red` = length of an un-split reduction: the tensor core adds into its fp32 accumulator with truncation, so
 // the error grows linearly with the chain (measured vs float64: 2.6e-6 at 1024, 1.2e-5 at 4096); chains longer
-// than DDNN_TF32_MAX_CHAIN stay on FFMA (forward / dX) or get more splits (dW).
+// than DDNN_TF32_MAX_CHAIN per accumulator set (the narrow tiles rotate their k-blocks over 4 or 2 sets) stay on
+// FFMA (forward / dX) or get more splits (dW).
 static bool use_tf32(int dtype, int64_t B, int64_t K, int64_t N, int64_t red, std::initializer_list<const void*> ptrs) {
   if (g_engine.load() == DDNN_ENGINE_SIMT || dtype != DDNN_F32 || g_f32_tc.load() != 2) return false;
-  if (!tf32_shape_ok(B, K, N) || red > DDNN_TF32_MAX_CHAIN) return false;
+  if (!tf32_shape_ok(B, K, N) || red > tf32_max_reduction(B, N)) return false;
   for (const void* p : ptrs)
     if (p && !aligned16(p)) return false;
   return true;

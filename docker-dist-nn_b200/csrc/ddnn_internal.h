@@ -87,6 +87,7 @@ int tail2_launch(const float* A1, const float* W2, const float* b2, const float*
 // ---- fp32 operands on tcgen05 as error-compensated TF32 (ddnn_tf32.cu) -----------------
 constexpr int64_t DDNN_TF32_MAX_CHAIN = 2048;  // longest reduction accumulated in one TMEM accumulator
 bool tf32_shape_ok(int64_t B, int64_t K, int64_t N);
+int64_t tf32_max_reduction(int64_t M, int64_t N);  // forward / dX with an (M x N) output: longest reduction taken
 int tf32_forward(const float* X, const float* W, const float* bias, float* A, int64_t B, int64_t K, int64_t N,
                  int act, cudaStream_t st);
 int tf32_dx(const float* dZ, const float* W, const float* Aprev, float* dZprev, int64_t B, int64_t K, int64_t N,

@@ -440,6 +440,13 @@ bool tf32_shape_ok(int64_t B, int64_t K, int64_t N) {
   return B > 0 && K >= 32 && N >= 32 && K % 4 == 0 && N % 4 == 0;
 }
 
+// longest un-split reduction the forward / dX GEMM with an (M x N) output accepts: DDNN_TF32_MAX_CHAIN per
+// accumulator set of the tile width pick_bn chooses
+int64_t tf32_max_reduction(int64_t M, int64_t N) {
+  const int bn = pick_bn(M, N);
+  return DDNN_TF32_MAX_CHAIN * (bn == 32 ? TCfg<32>::NACC_FWD : (bn == 64 ? TCfg<64>::NACC_FWD : TCfg<128>::NACC_FWD));
+}
+
 int tf32_forward(const float* X, const float* W, const float* bias, float* A, int64_t B, int64_t K, int64_t N, int act,
                  cudaStream_t st) {
   // D[B, N] = X[B, K] . W[K, N]: A operand K-major, B operand MN-major (W is [K][N] like grpc_node.py:51)
