@@ -174,6 +174,7 @@ struct EpiDx {  // dZprev = acc * f'(Aprev)
 struct EpiStoreF32 {  // raw fp32 store (gradient output or split-K partial)
   float* out;
   int64_t ld;
+  __device__ __forceinline__ void prefetch(int64_t, int) const {}
   __device__ __forceinline__ void apply4(int64_t row, int col, float4 v, int nv, bool vec) const {
     float* p = out + row * ld + col;
     if (vec && nv == 4) {
@@ -192,6 +193,9 @@ struct EpiSgd {  // W_master -= lr * acc ; shadow = bf16(W_master)
   bf16* shadow;  // nullable
   int64_t ld;
   float lr;
+  __device__ __forceinline__ void prefetch(int64_t row, int col) const {  // pulls the line towards L1 ahead of apply4
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(w + row * ld + col));
+  }
   __device__ __forceinline__ void apply4(int64_t row, int col, float4 v, int nv, bool vec) const {
     float* p = w + row * ld + col;
     if (vec && nv == 4) {

@@ -33,17 +33,20 @@ reduce_dw_kernel(const float* __restrict__ dw_part, const float* __restrict__ db
     const int splits = is_w ? splits_w : splits_b;  // the bias row may come from a different split plan
     float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
     if (active) {
-      int z = sub;
-      for (; z + 3 * G < splits; z += 4 * G) {
+      // the lane that will apply the update starts fetching its W (or bias) operand now, not after the reduction
+      if (sub == 0 && col < N) {
+        if (is_w) ew.prefetch(row, col);
+        else eb.prefetch(0, col);
+      }
+      // 4 split-loads per round, all issued before the first add (also in the last, partial round: a scalar tail
+      // loop would serialise its loads behind the adds)
+      for (int z = sub; z < splits; z += 4 * G) {
         float4 v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) v[u] = ld4(base + (int64_t)(z + u * G) * zs);
+        for (int u = 0; u < 4; ++u)
+          v[u] = (z + u * G < splits) ? ld4(base + (int64_t)(z + u * G) * zs) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
         for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
-      }
-      for (; z < splits; z += G) {
-        float4 v = ld4(base + (int64_t)z * zs);
-        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
       }
     }
 #pragma unroll
