@@ -44,6 +44,16 @@ def test_host_only_entry_points():
     assert rc == _lib.ERR_DIM and "bad dimensions" in _lib.last_error()
     rc = _lib.lib.ddnn_set_engine(9)
     assert rc == _lib.ERR_ARG
+    assert _lib.lib.ddnn_set_f32_tensor_cores(3) == _lib.ERR_ARG and "mode 3" in _lib.last_error()
+    assert _lib.lib.ddnn_set_f32_tensor_cores(_lib.F32_TC_DEFAULT) == 0 and _lib.lib.ddnn_set_pdl(1) == 0
+    # the fused two-layer tail only takes small fp32 shapes: capability query and status code, no GPU needed
+    assert _lib.lib.ddnn_tail2_workspace_bytes(4096, 128, 64, 10, _lib.F32) > 0
+    for bad in ((4096, 256, 64, 10, _lib.F32), (4096, 128, 128, 10, _lib.F32), (4096, 128, 64, 17, _lib.F32),
+                (4096, 126, 64, 10, _lib.F32), (4096, 128, 64, 10, _lib.BF16)):
+        assert _lib.lib.ddnn_tail2_workspace_bytes(*bad) == 0
+    rc = _lib.lib.ddnn_tail2_train(None, None, None, None, None, None, None, None, 1, 1, 4096, 256, 64, 10, 1.0, _lib.F32,
+                                   None, 0, None)
+    assert rc == _lib.ERR_UNSUPPORTED and "K1 <= 128" in _lib.last_error()
 
 
 def test_product_does_not_import_oracle():
