@@ -246,6 +246,21 @@ int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, voi
 
 static size_t np_of(int64_t N) { return (size_t)((N + 3) & ~(int64_t)3); }
 
+// Split count a deferred ddnn_output_layer_train wrote into a workspace, keyed by the workspace pointer:
+// ddnn_output_layer_finish reads the partials with THAT layout even if the engine switch was flipped in
+// between (the two calls are meant to be issued at different times on different streams).
+static std::mutex g_defer_mu;
+static std::map<const void*, int> g_defer_splits;
+static void defer_record(const void* ws, int splits) {
+  std::lock_guard<std::mutex> g(g_defer_mu);
+  g_defer_splits[ws] = splits;
+}
+static int defer_lookup(const void* ws, int fallback) {
+  std::lock_guard<std::mutex> g(g_defer_mu);
+  auto it = g_defer_splits.find(ws);
+  return it == g_defer_splits.end() ? fallback : it->second;
+}
+
 size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
   if (B <= 0 || K <= 0 || N <= 0) return 0;
   const size_t np = np_of(N);
@@ -391,7 +406,10 @@ int ddnn_output_layer_train(const void* A, const void* W, const int32_t* labels,
   rc = outlayer_fused(A, W, bias, labels, dZ, row_loss, dZprev, dw_part, db_part, B, K, N, act_prev, inv_denom, dtype,
                       st);
   if (rc) return rc;
-  if (apply == DDNN_OUTLAYER_DEFER) return DDNN_OK;  // ddnn_output_layer_finish reduces, on any stream
+  if (apply == DDNN_OUTLAYER_DEFER) {  // ddnn_output_layer_finish reduces, on any stream
+    defer_record(workspace, splits);
+    return DDNN_OK;
+  }
   if (loss) {
     rc = loss_reduce(row_loss, loss, B, inv_denom, accumulate_loss, st);
     if (rc) return rc;
@@ -424,7 +442,12 @@ int ddnn_output_layer_finish(const float* row_loss, float* loss, float* W_master
     return DDNN_ERR_WORKSPACE;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  const int splits = outlayer_splits(B, K, dtype);
+  const int splits = defer_lookup(workspace, outlayer_splits(B, K, dtype));  // what the deferred call wrote
+  if ((size_t)splits * ((size_t)K + 1) * np_of(N) * sizeof(float) > workspace_bytes) {
+    set_error("ddnn_output_layer_finish: the deferred call on this workspace used %d splits, which do not fit %zu bytes",
+              splits, workspace_bytes);
+    return DDNN_ERR_WORKSPACE;
+  }
   float* dw_part = (float*)workspace;
   float* db_part = dw_part + (size_t)splits * K * np_of(N);
   if (loss) {
@@ -440,8 +463,8 @@ struct Tail2Ws {
   float *dw2, *db2, *dw3, *db3;
   size_t bytes;
 };
-static Tail2Ws tail2_ws(void* ws, int64_t B, int64_t K1, int64_t N2, int64_t N3) {
-  const size_t S = (size_t)tail2_splits(B), np3 = np_of(N3);
+static Tail2Ws tail2_ws(void* ws, int64_t B, int64_t K1, int64_t N2, int64_t N3, int splits = 0) {
+  const size_t S = (size_t)(splits > 0 ? splits : tail2_splits(B)), np3 = np_of(N3);
   Tail2Ws w;
   w.dw2 = (float*)ws;
   w.db2 = w.dw2 + S * K1 * N2;
@@ -453,7 +476,8 @@ static Tail2Ws tail2_ws(void* ws, int64_t B, int64_t K1, int64_t N2, int64_t N3)
 
 size_t ddnn_tail2_workspace_bytes(int64_t B, int64_t K1, int64_t N2, int64_t N3, int dtype) {
   if (B <= 0 || !tail2_ok(K1, N2, N3, dtype)) return 0;
-  return tail2_ws(nullptr, B, K1, N2, N3).bytes;
+  // sized for the largest split count of ANY batch of at most B rows: one buffer serves a ragged last batch too
+  return tail2_ws(nullptr, B, K1, N2, N3, tail2_max_splits(B)).bytes;
 }
 
 int ddnn_tail2_train(const void* A1, const void* W2, const float* b2, const void* W3, const float* b3,

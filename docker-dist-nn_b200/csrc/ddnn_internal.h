@@ -78,6 +78,7 @@ int umma_dw(const bf16* X, const bf16* dZ, float* dw_part, int splits, float* W_
 // ---- fused last two layers of a small fp32 MLP (ddnn_tail2.cu) ----------------------------
 bool tail2_ok(int64_t K1, int64_t N2, int64_t N3, int dtype);
 int tail2_splits(int64_t B);
+int tail2_max_splits(int64_t B);  // bound over every batch of at most B rows
 int tail2_launch(const float* A1, const float* W2, const float* b2, const float* W3, const float* b3,
                  const int32_t* labels, float* dZ1, float* row_loss, float* dw2_part, float* db2_part,
                  float* dw3_part, float* db3_part, int64_t B, int64_t K1, int64_t N2, int64_t N3, int act1,

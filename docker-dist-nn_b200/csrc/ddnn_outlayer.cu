@@ -558,8 +558,13 @@ int outlayer_splits(int64_t B, int64_t K, int dtype) {
   if (g_outlayer_mma.load() && use_mma(K, dtype)) return mma_grid(B);
   return cdiv(B, rows_per_block(B));
 }
+// Bound on the split count of EVERY batch of at most B rows, over both variants: a caller sizes its workspace
+// once for its largest batch and then runs smaller (ragged last) batches through the same buffer, and
+// cdiv(B', rows_per_block(B')) is not monotone in B' (512 blocks at 65536 rows, 592 at 37888).  The FFMA variant
+// never has more than 4 x 148 blocks nor more blocks than 64-row tiles; the MMA grid grows with B.
 int outlayer_max_splits(int64_t B, int64_t K, int dtype) {
-  const int a = cdiv(B, rows_per_block(B));
+  const int64_t tiles = cdiv(B, (int64_t)TILE_ROWS);
+  const int a = (int)(tiles < 4 * 148 ? tiles : 4 * 148);
   const int b = use_mma(K, dtype) ? mma_grid(B) : 0;
   return a > b ? a : b;
 }

@@ -699,6 +699,13 @@ bool tail2_ok(int64_t K1, int64_t N2, int64_t N3, int dtype) {
          N3 >= 1 && N3 <= 16;
 }
 int tail2_splits(int64_t B) { return plan(B).grid; }
+// Bound on tail2_splits(B') for every B' <= B (workspace sizing): the grid is not monotone in the batch (147 CTAs
+// at 4096 rows, 148 at 3540), but it never exceeds the SM count nor the number of 4-row tiles.
+int tail2_max_splits(int64_t B) {
+  const int64_t t = (B + 3) / 4;
+  const int sms = sm_count();
+  return (int)(t < sms ? t : sms);
+}
 
 int tail2_launch(const float* A1, const float* W2, const float* b2, const float* W3, const float* b3,
                  const int32_t* labels, float* dZ1, float* row_loss, float* dw2_part, float* db2_part, float* dw3_part,

@@ -88,6 +88,9 @@ class LayerServiceServicer:
             if not input_list:
                 print(f"({lp.container_name}) Received empty input matrix.")
                 return Matrix()
+            if len({len(r) for r in input_list}) != 1:
+                # the reference's np.array/np.dot raise ValueError on ragged rows -> INVALID_ARGUMENT (grpc_node.py:149-153)
+                raise ValueError(f"({lp.container_name}) input rows have different lengths")
             output = lp.process_matrix(np.array(input_list))
             if lp.next_nodes:
                 nxt = lp.next_nodes[0]

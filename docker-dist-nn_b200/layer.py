@@ -127,6 +127,7 @@ class Layer:
         self._rows = 0
         self._bufs = None
         self._ws = None
+        self._ws_cache: Dict[int, Any] = {}
         self._gen = 0  # bumped whenever the batch buffers are reallocated (captured graphs go stale)
         self._probe = None  # bench.py: list collecting (name, start_event, end_event) per entry-point call
 
@@ -152,10 +153,11 @@ class Layer:
         CUDA fp32 tensor out.  Unknown ``func`` strings are the identity."""
         is_np = isinstance(values, np.ndarray)
         v = torch.as_tensor(values, dtype=torch.float32).to(self.device) if is_np else values.float()
-        squeeze = v.dim() == 1
-        v2 = (v.unsqueeze(0) if squeeze else v).contiguous()
+        # any rank, like numpy's ufuncs; softmax runs over the last axis (grpc_node.py:70-71, axis=-1)
+        shape = v.shape
+        v2 = v.reshape(-1, shape[-1] if v.dim() else 1).contiguous()
         out = ops.activate(v2, func) if v2.numel() else v2.clone()
-        out = out.squeeze(0) if squeeze else out
+        out = out.reshape(shape)
         return out.double().cpu().numpy() if is_np else out
 
     def _w(self, i: int) -> torch.Tensor:
@@ -201,6 +203,14 @@ class Layer:
         an output node (fp32), one dZ per local layer, the gradient handed upstream, the
         split-K workspace.  Buffers are reused while ``rows`` does not grow."""
         if self._bufs is not None and rows <= self._bufs["cap"]:
+            # split plans are not monotone in the batch (a ragged last batch can need MORE partials than the
+            # full one), so the scratch is re-checked for this row count and grown when it falls short
+            ws_bytes, ws2 = self._ws_need(rows)
+            if ws_bytes > self._ws.numel() or ws2 > self._ws_side.numel():
+                dev = self.device
+                self._ws = torch.empty((max(ws_bytes, self._ws.numel()),), dtype=torch.uint8, device=dev)
+                self._ws_side = torch.empty((max(ws2, self._ws_side.numel()),), dtype=torch.uint8, device=dev)
+                self._gen += 1
             self._rows = rows
             return
         dev, cdt = self.device, self._cdt
@@ -212,14 +222,7 @@ class Layer:
             last = i == len(lp) - 1
             a.append(torch.empty((rows, n), dtype=torch.float32 if (last and self.is_output) else cdt, device=dev))
             dz.append(torch.empty((rows, n), dtype=cdt, device=dev))
-        ws_bytes = max(ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp)
-        ws_bytes = max(ws_bytes, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0],
-                                                                  lp[-1]["weights"].shape[1], cdt))
-        tail_bytes = 0
-        if len(lp) >= 2 and self.is_output:
-            tail_bytes = ops.tail2_workspace_bytes(rows, lp[-2]["weights"].shape[0], lp[-2]["weights"].shape[1],
-                                                   lp[-1]["weights"].shape[1], cdt)
-        ws_bytes = max(ws_bytes, tail_bytes)
+        ws_bytes, ws2 = self._ws_need(rows)
         self._bufs = {
             "cap": rows, "a": a, "dz": dz,
             "dx": torch.empty((rows, lp[0]["weights"].shape[0]), dtype=cdt, device=dev),
@@ -227,15 +230,26 @@ class Layer:
             "loss": torch.zeros((1,), dtype=torch.float32, device=dev),
         }
         self._ws = torch.empty((max(ws_bytes, 256),), dtype=torch.uint8, device=dev)
-        # second workspace: the side-stream dW GEMMs of backward_and_step must not share scratch with dW_1
-        ws2 = max([ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp[1:]],
-                  default=0)
-        # ... and it holds the output layer's split partials when their reduction is deferred to the side stream
-        ws2 = max(ws2, tail_bytes, ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0],
-                                                                    lp[-1]["weights"].shape[1], cdt))
         self._ws_side = torch.empty((max(ws2, 256),), dtype=torch.uint8, device=dev)
         self._rows = rows
         self._gen += 1
+
+    def _ws_need(self, rows: int):
+        """Bytes of split-K scratch a step over ``rows`` rows needs: (main stream, side stream).  The side
+        workspace serves the dW GEMMs of the upper layers, which run beside dW_1 in ``backward_and_step`` and
+        must not share its scratch, and the deferred reductions of the fused output layer / two-layer tail."""
+        hit = self._ws_cache.get(rows)
+        if hit is not None:
+            return hit
+        lp, cdt = self.layer_params, self._cdt
+        dw = [ops.dw_workspace_bytes(rows, p["weights"].shape[0], p["weights"].shape[1], cdt) for p in lp]
+        out_b = ops.output_layer_workspace_bytes(rows, lp[-1]["weights"].shape[0], lp[-1]["weights"].shape[1], cdt)
+        tail_b = 0
+        if len(lp) >= 2 and self.is_output:
+            tail_b = ops.tail2_workspace_bytes(rows, lp[-2]["weights"].shape[0], lp[-2]["weights"].shape[1],
+                                               lp[-1]["weights"].shape[1], cdt)
+        self._ws_cache[rows] = (max(max(dw), out_b, tail_b), max(max(dw[1:], default=0), out_b, tail_b))
+        return self._ws_cache[rows]
 
     def input_buffer(self, row0: int, rows: int) -> torch.Tensor:
         """Rows [row0, row0+rows) of this node's input activation buffer (receive target)."""

@@ -45,6 +45,8 @@ def dense_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, act, out
         od = out_dtype or (torch.float32 if act_id == ACT_SOFTMAX else x.dtype)
         out = torch.empty((b, n), dtype=od, device=x.device)
     _req(out, name="out")
+    if tuple(out.shape) != (b, n):  # out may be a neighbour GPU's buffer: never hand a mismatched slice to the kernel
+        raise ValueError(f"dense_forward: out has shape {tuple(out.shape)}, expected {(b, n)}")
     with torch.cuda.device(x.device):
         check(lib.ddnn_dense_forward(_p(x), _p(w), _p(bias), _p(out), b, k, n, act_id, _DT[x.dtype], _DT[out.dtype],
                                      _stream(x)))
@@ -100,6 +102,10 @@ def dense_backward_dx(dz: torch.Tensor, w: torch.Tensor, a_prev: Optional[torch.
     if out is None:
         out = torch.empty((b, k), dtype=dz.dtype, device=dz.device)
     _req(out, dz.dtype, "out")
+    if tuple(out.shape) != (b, k):
+        raise ValueError(f"dense_backward_dx: out has shape {tuple(out.shape)}, expected {(b, k)}")
+    if a_prev is not None and act_id != ACT_LINEAR and tuple(a_prev.shape) != (b, k):
+        raise ValueError(f"dense_backward_dx: a_prev has shape {tuple(a_prev.shape)}, expected {(b, k)}")
     with torch.cuda.device(dz.device):
         check(lib.ddnn_dense_backward_dx(_p(dz), _p(w), _p(a_prev if act_id != ACT_LINEAR else None), _p(out), b, k,
                                          n, act_id, _DT[dz.dtype], _stream(dz)))

@@ -374,3 +374,27 @@ def test_narrow_configuration_tracks_oracle_at_full_size(cuda_device):
         # the UPDATE itself (difference to the initial weights), not just the weights it barely moves
         assert rel_err(g["weights"] - b0["weights"], r["weights"] - b0["weights"]) < 0.1
         assert rel_err(g["biases"] - b0["biases"], r["biases"] - b0["biases"]) < 0.1
+
+
+@pytest.mark.parametrize("dtype,dims,cap,tail", [("f32", [784, 128, 64, 10], 4096, 3540),
+                                                 ("f32", [784, 128, 64, 10], 4096, 1249),
+                                                 ("bf16", [784, 256, 256, 10], 65536, 36000)])
+def test_ragged_last_batch_needs_more_split_partials(cuda_device, dtype, dims, cap, tail):
+    """Split plans are not monotone in the batch: the fused two-layer tail runs 147 CTAs at 4096 rows and 148 at
+    3540, the fused bf16 output layer 512 blocks at 65536 rows and up to 592 around 36000, the tf32 split-K dW more
+    splits at 1249 rows than at 4096.  A full batch followed by such a ragged last one (the order of
+    run_grpc_inference.py:198-205) must run through the buffers sized for the full batch -- and agree with the
+    oracle -- instead of failing with DDNN_ERR_WORKSPACE."""
+    from ddnn_b200 import Trainer
+    acts = ["relu", "relu", "softmax"]
+    ref = [dict(p) for p in make_params(dims, acts, seed=1)]
+    t = Trainer(make_params(dims, acts, seed=1), dtype=dtype)
+    x, y = synthetic_batch(cap + tail, dims[0], dims[-1], seed=0)
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    tol = F32_TOL if dtype == "f32" else 2e-2
+    for (a, b) in ((0, cap), (cap, cap + tail)):
+        got = t.train_step(xd[a:b], yd[a:b], 0.05).item()
+        want = oracle.train_step(ref, x[a:b], y[a:b], 0.05)
+        assert abs(got - want) < tol * want
+    for g, r in zip(t.export_params(), ref):
+        assert rel_err(g["weights"], r["weights"]) < (F32_TOL if dtype == "f32" else BF16_ACT_TOL)
