@@ -128,6 +128,7 @@ class Layer:
         self._bufs = None
         self._ws = None
         self._ws_cache: Dict[int, Any] = {}
+        self._a0_ext: Optional[torch.Tensor] = None  # caller's batch read in place as layer 1's operand
         self._gen = 0  # bumped whenever the batch buffers are reallocated (captured graphs go stale)
         self._probe = None  # bench.py: list collecting (name, start_event, end_event) per entry-point call
 
@@ -255,6 +256,27 @@ class Layer:
         """Rows [row0, row0+rows) of this node's input activation buffer (receive target)."""
         return self._bufs["a"][0][row0:row0 + rows]
 
+    def _a(self, i: int) -> torch.Tensor:
+        """Input of local layer i for the whole batch: the caller's own tensor for layer 1 when it was
+        adopted (``set_input``), else the node's buffer."""
+        if i == 0 and self._a0_ext is not None:
+            return self._a0_ext
+        return self._bufs["a"][i]
+
+    def set_input(self, x: Optional[torch.Tensor]) -> bool:
+        """Makes layer 1 (forward and dW_1, its only readers) read the batch straight from the caller's
+        tensor instead of a copy in ``input_buffer``: saves one read + one write of the batch per step.
+        Taken when ``x`` has the compute dtype, is contiguous and 16-byte aligned; the caller keeps it
+        unchanged until the step's weight update has run.  Returns whether it was adopted; ``None`` (or a
+        tensor that does not qualify) goes back to the internal buffer."""
+        ok = (x is not None and x.dtype == self._cdt and x.dim() == 2 and x.is_contiguous()
+              and x.data_ptr() % 16 == 0 and x.device == self.device)
+        if ok and x.shape[1] != self.expected_input_dim:
+            raise ValueError(f"({self.container_name}) Layer 1: expected input dim {self.expected_input_dim}, "
+                             f"got {x.shape[1]}")
+        self._a0_ext = x if ok else None
+        return ok
+
     def grad_buffer(self, row0: int, rows: int) -> torch.Tensor:
         """Rows of dZ of the LAST local layer (receive target for the downstream gradient)."""
         return self._bufs["dz"][-1][row0:row0 + rows]
@@ -276,11 +298,15 @@ class Layer:
             if x.shape[1] != self.expected_input_dim:
                 raise ValueError(f"({self.container_name}) Layer 1: expected input dim {self.expected_input_dim}, "
                                  f"got {x.shape[1]}")
-            dst = a[0][row0:row0 + rows]
-            if x.dtype == self._cdt:
-                dst.copy_(x)
+            if row0 == 0 and rows == self._rows and self.set_input(x):
+                pass  # the whole batch in the compute dtype: read in place, no staging copy
             else:
-                ops.cast(x.contiguous(), self._cdt, out=dst)
+                self._a0_ext = None
+                dst = a[0][row0:row0 + rows]
+                if x.dtype == self._cdt:
+                    dst.copy_(x)
+                else:  # the cast is the one pass that moves the batch into the node
+                    ops.cast(x.contiguous(), self._cdt, out=dst)
         n_layers = len(self.layer_params)
         for i, p in enumerate(self.layer_params):
             last = i == n_layers - 1
@@ -296,7 +322,7 @@ class Layer:
             k_, n_ = p["weights"].shape
             dst = out_target if (last and out_target is not None) else a[i + 1][row0:row0 + rows]
             with self._span(f"forward L{i + 1} {k_}->{n_}"):
-                ops.dense_forward(a[i][row0:row0 + rows], self._w(i), p["biases"], act, out=dst)
+                ops.dense_forward(self._a(i)[row0:row0 + rows], self._w(i), p["biases"], act, out=dst)
         return out_target if out_target is not None else a[-1][row0:row0 + rows]
 
     def loss_and_grad(self, labels: torch.Tensor, row0: int = 0, denom: Optional[int] = None,
@@ -332,7 +358,7 @@ class Layer:
         k_, n_ = self.layer_params[0]["weights"].shape
         dst = dx_target if dx_target is not None else b["dx"][sl]  # dx_target: the upstream stage's dZ buffer (peer)
         with self._span(f"dX L1 {n_}->{k_}"):
-            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), b["a"][0][sl], self.input_activation, out=dst)
+            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), self._a(0)[sl], self.input_activation, out=dst)
         return dst
 
     def step(self, lr: float, rows: Optional[int] = None) -> None:
@@ -343,7 +369,7 @@ class Layer:
         for i, p in enumerate(self.layer_params):
             k_, n_ = p["weights"].shape
             with self._span(f"dW+SGD L{i + 1} {k_}x{n_}"):
-                ops.dense_backward_dw_sgd(b["a"][i][:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
+                ops.dense_backward_dw_sgd(self._a(i)[:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
                                           w_shadow=self._shadow[i], workspace=self._ws)
 
     def backward_and_step(self, lr: float, rows: Optional[int] = None, side: Optional[torch.cuda.Stream] = None,
@@ -376,7 +402,7 @@ class Layer:
         p = self.layer_params[0]
         k_, n_ = p["weights"].shape
         with self._span(f"dW+SGD L1 {k_}x{n_}"):
-            ops.dense_backward_dw_sgd(b["a"][0][sl], b["dz"][0][sl], p["weights"], p["biases"], lr,
+            ops.dense_backward_dw_sgd(self._a(0)[sl], b["dz"][0][sl], p["weights"], p["biases"], lr,
                                       w_shadow=self._shadow[0], workspace=self._ws)
         main.wait_stream(side)
 
@@ -392,7 +418,7 @@ class Layer:
         if prev_act == "softmax":
             return False
         k, n = p["weights"].shape
-        return ops.output_layer_supported(self._bufs["a"][-2], k, n)
+        return ops.output_layer_supported(self._a(len(self.layer_params) - 1), k, n)
 
     def output_layer_step(self, labels: torch.Tensor, lr: float, rows: Optional[int] = None,
                           denom: Optional[int] = None, need_input_grad: bool = True,
@@ -420,12 +446,12 @@ class Layer:
         main = torch.cuda.current_stream(self.device)
         if side is None or side == main:
             with self._span(f"output layer fused {k_}->{n_}"):
-                ops.output_layer_train(b["a"][i][:rows], self._w(i), labels, b["row_loss"][:rows], b["loss"], inv,
+                ops.output_layer_train(self._a(i)[:rows], self._w(i), labels, b["row_loss"][:rows], b["loss"], inv,
                                        prev_act, self._ws, w_master=p["weights"], bias=p["biases"], lr=lr,
                                        w_shadow=self._shadow[i], dz=b["dz"][i][:rows], dz_prev=dz_prev)
             return b["loss"]
         with self._span(f"output layer fused {k_}->{n_}"):
-            ops.output_layer_train(b["a"][i][:rows], self._w(i), labels, b["row_loss"][:rows], None, inv, prev_act,
+            ops.output_layer_train(self._a(i)[:rows], self._w(i), labels, b["row_loss"][:rows], None, inv, prev_act,
                                    self._ws_side, bias=p["biases"], dz=b["dz"][i][:rows], dz_prev=dz_prev, defer=True)
         ev = torch.cuda.Event()
         ev.record(main)
@@ -477,7 +503,7 @@ class Layer:
         dz1 = b["dz"][i2 - 1][:rows] if i2 > 0 else (b["dx"][:rows] if need_input_grad else None)
         k1, n2 = p2["weights"].shape
         with self._span(f"tail fused {k1}->{n2}->{p3['weights'].shape[1]}"):
-            ops.tail2_train(b["a"][i2][:rows], p2["weights"], p2["biases"], p3["weights"], p3["biases"], labels,
+            ops.tail2_train(self._a(i2)[:rows], p2["weights"], p2["biases"], p3["weights"], p3["biases"], labels,
                             b["row_loss"][:rows], 1.0 / float(rows if denom is None else denom), act1,
                             p2["activation"], self._ws if ws is None else ws, dz1=dz1)
 
@@ -494,7 +520,7 @@ class Layer:
         """[(dW, db)] per local layer from the buffered activations/gradients (no update)."""
         rows = self._rows if rows is None else rows
         b = self._bufs
-        return [ops.dense_backward_dw(b["a"][i][:rows], b["dz"][i][:rows], workspace=self._ws)
+        return [ops.dense_backward_dw(self._a(i)[:rows], b["dz"][i][:rows], workspace=self._ws)
                 for i in range(len(self.layer_params))]
 
     def zero_loss(self) -> None:

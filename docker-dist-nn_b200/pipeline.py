@@ -140,6 +140,7 @@ class PipelineStage:
         t = self._t
         with torch.cuda.device(L.device):
             # ---- forward: the last local layer's epilogue stores into the next GPU's input buffer ----
+            in_place = self.first and self._adopt_input(x)
             for m, (r0, r1) in enumerate(slices):
                 n = r1 - r0
                 if not self.first:
@@ -147,7 +148,7 @@ class PipelineStage:
                 if not self.last and m == 0 and t > 1:
                     self._flag_wait(2 * M, t - 1)            # rank+1 is done with my step t-1 activations
                 tgt = None if self.last else P["next_a0"][r0:r1]
-                L.forward_train(x[r0:r1] if self.first else None, r0, n, out_target=tgt)
+                L.forward_train(x[r0:r1] if (self.first and not in_place) else None, r0, n, out_target=tgt)
                 if not self.last:
                     self._flag_write(P["next_flags"], m, t)
             # ---- backward: the dX epilogue stores dZ into the previous GPU's gradient buffer ----
@@ -172,6 +173,12 @@ class PipelineStage:
                 self._flag_write(P["next_flags"], 2 * M + 1, t)  # consumed rank+1's gradients
         return loss
 
+    def _adopt_input(self, x) -> bool:
+        """First stage: let layer 1 read the batch where the caller keeps it (no staging copy) when the
+        stage offers that (``Layer.set_input``) and the tensor qualifies."""
+        setter = getattr(self.layer, "set_input", None)
+        return bool(setter(x)) if setter is not None else False
+
     def _send(self, t: torch.Tensor, dst: int) -> None:
         dist.send(t, dst=dst, group=self.group)
 
@@ -188,10 +195,11 @@ class PipelineStage:
         L.begin_batch(rows)
         slices = micro_batch_slices(rows, micro_batches)
         # ---- forward: fill ----
+        in_place = self.first and self._adopt_input(x)
         for (r0, r1) in slices:
             n = r1 - r0
             if self.first:
-                out = L.forward_train(x[r0:r1], r0)
+                out = L.forward_train(None, r0, n) if in_place else L.forward_train(x[r0:r1], r0)
             else:
                 self._recv(L.input_buffer(r0, n), self.rank - 1)
                 out = L.forward_train(None, r0, n)

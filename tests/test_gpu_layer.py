@@ -398,3 +398,28 @@ def test_ragged_last_batch_needs_more_split_partials(cuda_device, dtype, dims, c
         assert abs(got - want) < tol * want
     for g, r in zip(t.export_params(), ref):
         assert rel_err(g["weights"], r["weights"]) < (F32_TOL if dtype == "f32" else BF16_ACT_TOL)
+
+
+@pytest.mark.parametrize("dtype,dims", [("f32", [784, 128, 64, 10]), ("bf16", [784, 256, 256, 10])])
+def test_input_batch_is_read_in_place(cuda_device, dtype, dims):
+    """Layer 1 (forward and dW_1) reads the caller's batch where it lies when it has the compute dtype (no
+    device-to-device staging copy); a batch that cannot be adopted (here: a strided view) still goes through the
+    node's own buffer.  Both routes give the same bits."""
+    from ddnn_b200 import Trainer
+    acts = ["relu", "relu", "softmax"]
+    cdt = torch.float32 if dtype == "f32" else torch.bfloat16
+    x, y = synthetic_batch(512, dims[0], dims[-1], seed=5)
+    xd, yd = to_dev(x).to(cdt).contiguous(), to_dev(y, torch.int32)
+    wide = torch.zeros((512, dims[0] + 16), dtype=cdt, device=xd.device)
+    wide[:, :dims[0]] = xd
+    strided = wide[:, :dims[0]]
+    assert not strided.is_contiguous()
+    t_in, t_cp = (Trainer(make_params(dims, acts, seed=1), dtype=dtype) for _ in range(2))
+    for _ in range(3):
+        l_in = t_in.train_step(xd, yd, 0.05).item()
+        assert t_in.layer._a0_ext is xd
+        l_cp = t_cp.train_step(strided, yd, 0.05).item()
+        assert t_cp.layer._a0_ext is None
+        assert l_in == l_cp
+    for a, b in zip(t_in.export_params(), t_cp.export_params()):
+        assert np.array_equal(a["weights"], b["weights"]) and np.array_equal(a["biases"], b["biases"])
