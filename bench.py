@@ -3,17 +3,20 @@
 layer hot path on N B200s.
 
     python bench.py --gpus 1 --steps K --warmup W              # our arm
-    python bench.py --impl reference --gpus 1 --steps K ...     # CPU arm (the oracle port)
+    python bench.py --impl reference --gpus 1 --steps K ...     # CPU arm (oracle port + the reference's own forward)
     torchrun --nproc-per-node N ... bench.py --gpus N ...       # one rank per GPU
 
 A "step" is one pass of the hot path over one batch of synthetic, seeded data.  Default
-workload = BASELINE.json configs[1]: the MNIST FCNN 784-128-64-10, batch 4096, fp32 path.
-At N > 1 that net is too small to pipeline: every rank trains an
-independent replica on its own batches ("weak" scaling, no data-path collective).  The
-layer-per-GPU pipeline over NCCL send/recv is exercised on the wide bf16 nets and reported
-in the ``pipeline`` object of the same JSON line (config 3: 4x8192; config 4: 8x16384, 32
-micro-batches) -- at N = 1 the same nets run as one stage, which is the denominator of the
-pipeline's scaling efficiency.
+workload = BASELINE.json configs[3], the config the metric's "% of bf16 tensor peak" and the
+north_star's 8-GPU scaling target are quoted on: the 8-layer 16384-wide bf16 FCNN, batch 65536
+in 32 micro-batches.  It fits one B200 (one stage holding all 8 layers), and at N = 2 / 4 / 8 the
+SAME batch runs through the layer-per-GPU pipeline ("strong" scaling): the per-N values of the
+driver's scaling run are the pipeline's scaling curve, and the first losses and a weight checksum
+in the line are the same bits at every N.  `roofline` is the tensor-core fraction of the
+dominant GEMM.  The small nets (configs[1] MNIST batch 4096 fp32, configs[4] narrow batch 65536
+bf16: HBM roofline) and configs[2] (4x8192) are reported in `extras`, each with value, e2e and
+roofline.  `--workload mnist4096|narrow65536|wide4x8192` makes one of them the headline; the MNIST-sized
+nets are too small to pipeline and run as independent replicas at N > 1.
 
 One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every key.
 """
@@ -29,6 +32,25 @@ import time
 REPO = os.path.dirname(os.path.abspath(__file__))
 if REPO not in sys.path:
     sys.path.insert(0, REPO)
+
+
+
+def _host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa: BLE001
+        return os.cpu_count() or 1
+
+
+if "--impl" in sys.argv and "reference" in sys.argv and os.environ.get("DDNN_REF_REEXEC") != "1":
+    # The CPU arm uses every host thread.  torch.distributed.run exports OMP_NUM_THREADS=1 to its workers,
+    # and BLAS reads the thread count when numpy is first imported, so fix the environment and start over.
+    if int(os.environ.get("RANK", "0")) != 0:
+        sys.exit(0)  # rank 0 alone runs the CPU arm; the other ranks exit without work
+    _n = str(_host_threads())
+    os.environ.update({"OMP_NUM_THREADS": _n, "OPENBLAS_NUM_THREADS": _n, "MKL_NUM_THREADS": _n,
+                       "DDNN_REF_REEXEC": "1"})
+    os.execv(sys.executable, [sys.executable] + sys.argv)
 
 import numpy as np  # noqa: E402
 
@@ -137,50 +159,117 @@ def cpu_threads() -> int:
     return os.cpu_count() or 1
 
 
+DEFAULT_WORKLOAD = "wide8x16384"
+LR = 0.01
+# rows of one CPU step (a bounded sample of the workload's batch): the oracle's float64 GEMMs are compute-bound
+# from ~100 rows on, and 20 + 5 steps must end within minutes on the host cores
+CPU_ROWS = {"mnist4096": 4096, "narrow65536": 8192, "wide4x8192": 256, "wide8x16384": 128}
+
+
+def line_config(workload: str, world: int):
+    """The `config` object of the JSON line -- the same for both arms (`--impl reference` reports on our config)."""
+    dims, acts, rows, dtype, micro = WORKLOADS[workload]
+    pipe = workload.startswith("wide")
+    n_layers = len(acts)
+    if pipe:
+        par = "single (all layers on one GPU)" if world == 1 else f"pipeline{world} ({n_layers // world} layers per GPU)"
+        l2 = f"one batch = {rows * dims[0] * 2 / 2**20:.0f} MiB of inputs, {n_layers * dims[1] * dims[1] * 2 / 2**20:.0f}" \
+             f" MiB of bf16 weights > 126 MiB L2"
+    else:
+        par = "single" if world == 1 else f"replicas{world} (net too small to pipeline)"
+        l2 = "inputs rotate over distinct resident batches totalling >= 2 x 126 MiB L2"
+    return {"workload": workload, "dims": dims, "activations": acts, "rows_per_step": rows, "micro_batches": micro,
+            "lr": LR, "parallelism": par, "l2": l2}
+
+
 def cpu_train_samples_per_s(workload: str, budget_s: float, steps=None, warmup=1, rows_cap=None):
     """Times oracle.train_step (numpy float64, multi-threaded BLAS) on the host cores on a
     bounded sample of the workload.  Returns (samples/s, description, ms_per_step, steps)."""
     import oracle
     from ddnn_b200.config import make_params, synthetic_batch
     dims, acts, rows, _, _ = WORKLOADS[workload]
-    if rows_cap:
-        rows = min(rows, rows_cap)
+    rows = min(rows, rows_cap or CPU_ROWS[workload])
+    note = ""
+    try:  # float64 weights + gradients + the updated copy of the 16384-wide net: ~3 x 17 GB
+        import psutil
+        need = 3.2 * 8 * sum(k * n for k, n in zip(dims[:-1], dims[1:]))
+        if need > 0.6 * psutil.virtual_memory().available:
+            keep = max(2, int(len(acts) * 0.6 * psutil.virtual_memory().available / need))
+            note = f"; host RAM holds {keep} of the {len(acts)} layers in float64: timed on the last {keep}, " \
+                   f"samples/s scaled by their share of the step's FLOPs"
+            scale = flops_per_sample(dims[-(keep + 1):]) / flops_per_sample(dims)
+            dims, acts = dims[-(keep + 1):], acts[-keep:]
+        else:
+            scale = 1.0
+    except Exception:  # noqa: BLE001
+        scale = 1.0
     params = make_params(dims, acts, seed=1)
     x, y = synthetic_batch(rows, dims[0], dims[-1], seed=0)
     for _ in range(max(0, warmup)):
-        oracle.train_step(params, x, y, 0.01)
+        oracle.train_step(params, x, y, LR)
     t0 = time.perf_counter()
     n = 0
     while True:
-        oracle.train_step(params, x, y, 0.01)
+        oracle.train_step(params, x, y, LR)
         n += 1
         el = time.perf_counter() - t0
         if (steps is not None and n >= steps) or (steps is None and el >= budget_s):
             break
-    desc = f"{n} oracle train steps (numpy float64) of {workload} at {rows} rows/step"
-    return rows * n / el, desc, 1e3 * el / n, n
+    desc = f"{n} oracle train steps (numpy float64, {cpu_threads()} BLAS threads) of {workload} at {rows} rows/step{note}"
+    return scale * rows * n / el, desc, 1e3 * el / n, n
+
+
+def reference_forward_baselines(budget_s: float):
+    """the reference's OWN code (unmodified copy under baseline/_ref), forward-only, on
+    the MNIST FCNN it ships scripts for (BASELINE.json configs[0]).  None when the copy is absent."""
+    sys.path.insert(0, os.path.join(REPO, "tools"))
+    try:
+        import reference_chain as rc
+    except Exception:  # noqa: BLE001
+        return None
+    if not rc.available():
+        return {"unavailable": "baseline/_ref is empty (run tools/install_reference.py where /root/reference exists)"}
+    from ddnn_b200.config import make_params, synthetic_batch
+    dims, acts = WORKLOADS["mnist4096"][0], WORKLOADS["mnist4096"][1]
+    params = make_params(dims, acts, seed=1)
+    x, _ = synthetic_batch(2560, dims[0], dims[-1], seed=0)
+    out = {"model": "784-128-64-10 (configs[0])", "kind": "reference", "cores": cpu_threads(),
+           "what": "forward only -- the reference has no backward pass"}
+    try:
+        v2, calls = rc.time_in_process(params, x, 640, budget_s)
+        out["B2_in_process_layer"] = {"value": v2, "unit": "inference samples/s",
+                                      "sample": f"{calls} Layer.process_matrix calls of 640 rows, float64"}
+    except Exception as e:  # noqa: BLE001
+        out["B2_in_process_layer"] = {"error": repr(e)[:200]}
+    try:
+        v1, rpcs, rpr, _ = rc.time_grpc_chain(params, x, 640, budget_s)
+        out["B1_grpc_chain"] = {"value": v1, "unit": "inference samples/s",
+                                "sample": f"{rpcs} RPCs of {rpr} rows (under the 4 MiB server cap) through 3 unmodified "
+                                          f"grpc_node.py processes on localhost, reference client loop"}
+    except Exception as e:  # noqa: BLE001
+        out["B1_grpc_chain"] = {"error": repr(e)[:200]}
+    return out
 
 
 def run_reference_arm(args):
-    rank = int(os.environ.get("RANK", "0"))
-    if rank != 0:
-        return  # other ranks exit 0 without work
-    workload = args.workload or "mnist4096"
-    # each step a bounded sample: cap rows so that K steps finish within minutes on host cores
-    cap = {"mnist4096": 4096, "narrow65536": 8192, "wide4x8192": 64, "wide8x16384": 16}[workload]
-    v, desc, ms, n = cpu_train_samples_per_s(workload, 0.0, steps=max(1, args.steps), warmup=max(0, args.warmup),
-                                             rows_cap=cap)
-    dims = WORKLOADS[workload][0]
+    """CPU arm on the box's host cores (rank 0 only; the re-exec at the top of this file gave BLAS every
+    thread).  The line's value is the float64 training port of the oracle on a bounded sample of OUR arm's
+    config (the reference has no training code); `reference_forward` adds the reference's own
+    forward path: the gRPC chain (B1) and the in-process Layer (B2)."""
+    workload = args.workload or DEFAULT_WORKLOAD
+    v, desc, ms, n = cpu_train_samples_per_s(workload, 0.0, steps=max(1, args.steps), warmup=max(0, args.warmup))
     line = {
         "impl": "reference", "metric": "train samples/sec (fwd+bwd+SGD)", "value": v, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": n, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload, "dims": dims, "rows_per_step": min(WORKLOADS[workload][2], cap)},
+        "scaling": "strong" if workload.startswith("wide") else "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": line_config(workload, args.gpus),
         "cpu_baseline": {"value": v, "unit": "samples/s", "cores": cpu_threads(), "kind": "port", "sample": desc,
-                         "note": "the reference has no backward/SGD (SURVEY.md 0.1) and is Python that cannot "
-                                 "travel to the GPU box; this is the float64 numpy oracle pinned to it"},
+                         "note": "the reference has no backward/SGD (SURVEY.md 0.1): this is the float64 numpy oracle, "
+                                 "pinned bit-exact to the reference's forward"},
         "e2e": {"value": v, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
+    if not args.no_extra:
+        line["reference_forward"] = reference_forward_baselines(4.0)
     print(json.dumps(line), flush=True)
 
 
@@ -230,7 +319,7 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None):
     dtype = dtype or wdtype
     elt = 4 if dtype == "f32" else 2
     tr = Trainer(device_params(dims, acts, device), dtype=dtype, device=device, input_dim=dims[0])
-    tr.lr = 0.01
+    tr.lr = LR
     xdt = torch.float32 if dtype == "f32" else torch.bfloat16
     # inputs larger than L2: a pool of distinct resident batches, rotated every step
     batch_bytes = rows * dims[0] * elt
@@ -267,7 +356,8 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None):
     # the public call Trainer.train_step_host ----
     hx = [torch.rand((rows, dims[0]), dtype=torch.float32).pin_memory() for _ in range(4)]
     hy = [torch.randint(0, dims[-1], (rows,), dtype=torch.int32).pin_memory() for _ in range(4)]
-    e2e_steps = max(3, min(steps, 400))
+    # the host loop is PCIe-bound at ~1 ms per step or less: time enough steps for a stable figure
+    e2e_steps = max(200 if use_graph else 3, min(steps, 400))
     if use_graph:
         # Trainer.fit_stream: H2D of batch i+1 overlaps the step on batch i; every step's loss comes back
         tr.fit_stream([(hx[i & 3], hy[i & 3]) for i in range(4)])  # untimed: builds the two slot graphs
@@ -399,53 +489,201 @@ def kernel_roofline(tr, xs, ys, dtype, steps, device, use_graph):
     return rows_out
 
 
-def bench_pipeline(workload, steps, warmup, device, rank, world, barrier):
-    """Layer-per-GPU pipeline of a wide net over `world` GPUs (world = 1: one stage)."""
+def roofline_of(ks, dtype, peaks, workload, in_step: bool):
+    """`roofline` object for the entry point with the largest share of the step.  Tensor bound (bf16 GEMMs above
+    the ridge of 255 FLOP/B) against the measured cuBLAS bf16 rate -- the sustained figure for a kernel timed
+    inside a long step, the burst one for a kernel timed alone; HBM bound against the measured copy bandwidth."""
+    dom = max(ks, key=lambda r: r["ms"] * r.get("launches", 1))
+    tensor = dtype == "bf16" and dom["bytes"] > 0 and dom["flops"] / dom["bytes"] > 255
+    if tensor:
+        peak = peaks["bf16_tflops_sustained"] if in_step else peaks["bf16_tflops"]
+        roof = {"bound": "tensor", "achieved": dom["tflops"], "peak": peak, "unit": "TFLOP/s", "frac": dom["tflops"] / peak,
+                "peak_kind": "sustained (kernel timed inside a long step)" if in_step else "burst (kernel timed alone)",
+                "frac_of_burst": dom["tflops"] / peaks["bf16_tflops"]}
+    else:
+        roof = {"bound": "hbm", "achieved": dom["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                "frac": dom["gbs"] / peaks["hbm_gbs"]}
+    traffic = None
+    try:
+        with open(os.path.join(REPO, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(workload, {}).get(dom["kernel"])
+    except Exception:  # noqa: BLE001
+        pass
+    total = sum(r["ms"] * r.get("launches", 1) for r in ks)
+    roof.update({"traffic": traffic, "algorithmic_bytes": dom["bytes"], "algorithmic_flops": dom["flops"],
+                 "kernel": dom["kernel"], "ms_per_launch": dom["ms"], "launches_per_step": dom.get("launches", 1),
+                 "peak_source": peaks["source"], "kernel_tflops": dom["tflops"],
+                 "step_share": dom["ms"] * dom.get("launches", 1) / total, "timing": dom["how"]})
+    return roof
+
+
+def _compact(ks):
+    return [{k: (round(v, 6) if isinstance(v, float) else v) for k, v in r.items()
+             if k in ("kernel", "ms", "launches", "tflops", "gbs")} for r in ks]
+
+
+def small_net_entry(workload, dtype, steps, warmup, device, rank, world, barrier, max_over_ranks, peaks):
+    """A net that lives on one GPU (MNIST / narrow): device-resident value, e2e through Trainer.fit_stream,
+    per-entry-point roofline.  At world > 1 every rank trains its own replica (no data-path collective)."""
+    res, tr, xs, ys = bench_single(workload, dtype, steps, warmup, device, barrier)
+    ms_total = max_over_ranks(res["ms_total"])
+    e2e_ms = max_over_ranks(res["e2e_ms_total"])
+    dims, rows = res["dims"], res["rows"]
+    elt = 4 if res["dtype"] == "f32" else 2
+    value = world * rows * steps / (ms_total / 1e3)
+    fps = flops_per_sample(dims)
+    ent = {"workload": workload, "value": value, "unit": "samples/s", "ms_per_step": ms_total / steps, "steps": steps,
+           "scaling": "weak", "dtype": res["dtype"], "rows_per_step_per_gpu": rows, "cuda_graph": res["cuda_graph"],
+           "launches_per_step": int(res["launches_per_step"]),
+           "l2": f"inputs rotate over {res['pool_batches']} distinct resident batches "
+                 f"({res['pool_bytes'] / 2**20:.0f} MiB > 126 MiB L2)",
+           "tflops": value * fps / 1e12,
+           # SURVEY.md section 8d: activation bytes per sample x samples/s over the measured HBM peak
+           "step_hbm_bytes_per_sample": bytes_per_sample(dims, elt),
+           "step_hbm_frac_of_measured": value * bytes_per_sample(dims, elt) / (world * peaks["hbm_gbs"] * 1e9),
+           "e2e": {"value": world * rows * res["e2e_steps"] / (e2e_ms / 1e3), "unit": "samples/s",
+                   "h2d_bytes_per_step": res["h2d"], "d2h_bytes_per_step": res["d2h"], "steps": res["e2e_steps"],
+                   "api": res["e2e_api"]}}
+    if rank == 0:
+        ks = kernel_roofline(tr, xs, ys, res["dtype"], steps, device, res["cuda_graph"])
+        ent["roofline"] = roofline_of(ks, res["dtype"], peaks, workload, in_step=not res["cuda_graph"])
+        ent["kernels"] = _compact(ks)
+    del tr, xs, ys
+    return ent
+
+
+def wide_entry(workload, steps, warmup, device, rank, world, barrier, max_over_ranks, peaks, e2e_steps=4):
+    """A wide bf16 net through the layer-per-GPU pipeline on `world` GPUs (world = 1: one stage holds every
+    layer): the SAME global batch at every world size (strong scaling).  Besides the throughput, the first
+    losses and an exact checksum of the post-run weights are reported: the pipeline is built to give the same
+    bits at every stage count."""
     import torch
+    import torch.distributed as dist
     from ddnn_b200 import Layer, _lib
     from ddnn_b200.pipeline import PipelineStage, stage_assignment
     dims, acts, rows, dtype, micro = WORKLOADS[workload]
     n_layers = len(acts)
-    if world > n_layers:
-        return None
+    if world > n_layers or n_layers % world:
+        return {"workload": workload, "skipped": f"{n_layers} layers do not split over {world} GPUs"}
     lo, hi = stage_assignment(n_layers, world)[rank]
     # every rank draws the full parameter stream so that stage weights do not depend on `world`
     g = torch.Generator(device=device).manual_seed(1)
     params = []
     for i, (k, n, a) in enumerate(zip(dims[:-1], dims[1:], acts)):
         std = ((2.0 if a == "relu" else 1.0) / k) ** 0.5
+        w = torch.randn((k, n), device=device, generator=g, dtype=torch.float32) * std
         if lo <= i < hi:
-            w = torch.randn((k, n), device=device, generator=g, dtype=torch.float32) * std
             params.append({"weights": w, "biases": torch.full((n,), 0.01, device=device), "activation": a})
+        del w
     layer = Layer.from_params(params, dims[lo], container_name=f"stage{rank}", dtype=dtype, device=device,
                               input_activation=(acts[lo - 1] if lo > 0 else "linear"), is_output=(hi == n_layers))
-    transport = os.environ.get("DDNN_TRANSPORT", "peer") if world > 1 else "nccl"
-    stage = PipelineStage(layer, rank, world, transport=transport)
-    reserve = int(os.environ.get("DDNN_SM_RESERVE", "0")) if world > 1 else 0
-    _lib.set_sm_reserve(reserve)
-    gx = torch.Generator(device=device).manual_seed(0)
-    x = torch.rand((rows, dims[0]), device=device, generator=gx).to(torch.bfloat16) if rank == 0 else None
-    y = torch.randint(0, dims[-1], (rows,), device=device, generator=gx, dtype=torch.int32) if rank == world - 1 else None
+    del params
+    transport = os.environ.get("DDNN_TRANSPORT", "peer") if world > 1 else "local"
+    schedule = os.environ.get("DDNN_SCHEDULE", "gpipe")
+    stage = PipelineStage(layer, rank, world, transport=transport if world > 1 else "nccl", schedule=schedule)
+    first, last = rank == 0, rank == world - 1
+    # batch and labels from their own generators: the same data whatever the stage count
+    x = torch.rand((rows, dims[0]), device=device, generator=torch.Generator(device=device).manual_seed(0)
+                   ).to(torch.bfloat16) if first else None
+    y = torch.randint(0, dims[-1], (rows,), device=device, generator=torch.Generator(device=device).manual_seed(2),
+                      dtype=torch.int32) if last else None
     l0 = _lib.launch_count()
+    first_losses = []
 
-    def step(_i):
-        stage.train_step(x, y, rows, micro, 0.01)
-    ms = timed(step, steps, warmup, device, barrier)
+    def step(i):
+        loss = stage.train_step(x, y, rows, micro, LR)
+        if i < 3 and last:
+            first_losses.append(float(loss.item()))
+    ms = max_over_ranks(timed(step, steps, warmup, device, barrier))
     launches = (_lib.launch_count() - l0) // max(1, steps + warmup)
-    _lib.set_sm_reserve(0)
-    return {"sm_reserve": reserve, "transport": transport, "workload": workload, "rows": rows, "micro_batches": micro, "ms_total": ms, "dims": dims,
-            "launches_per_step": launches, "stages": world, "layers_here": hi - lo}
+    # exact, order-independent checksum of the fp32 master weights after warmup + steps updates
+    sums = [int(p["weights"].view(torch.int32).to(torch.int64).sum().item()) for p in layer.layer_params]
+    if world > 1:
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (sums, first_losses))
+        sums = [v for part in gathered for v in part[0]]
+        first_losses = gathered[-1][1]
+    value = rows * steps / (ms / 1e3)
+    fps = flops_per_sample(dims)
+    ent = {"workload": workload, "stages": world, "layers_per_stage": hi - lo, "micro_batches": micro,
+           "transport": transport, "schedule": schedule, "rows_per_step": rows, "steps": steps, "value": value,
+           "unit": "samples/s", "ms_per_step": ms / steps, "scaling": "strong", "dtype": dtype,
+           "launches_per_step": int(launches), "tflops_total": value * fps / 1e12,
+           "tensor_frac_of_measured_burst": value * fps / 1e12 / (world * peaks["bf16_tflops"]),
+           "tensor_frac_of_measured_sustained": value * fps / 1e12 / (world * peaks["bf16_tflops_sustained"]),
+           "bubble_bound": (3 * micro) / (3 * micro + 2 * (world - 1)),
+           "loss_first_steps": first_losses, "loss_first_steps_hex": [float(v).hex() for v in first_losses],
+           "weights_checksum": f"{sum(sums) & 0xFFFFFFFFFFFFFFFF:016x}",
+           "weights_checksum_per_layer": [f"{v & 0xFFFFFFFFFFFFFFFF:016x}" for v in sums],
+           "checksum_of": f"int64 sum of the fp32 master weights' bit patterns after {warmup + steps} steps"}
+    # ---- per-entry-point timing, in situ: CUDA events around every call inside 2 more steps (rank 0's stage) ----
+    layer._probe = []
+    for _ in range(2):
+        stage.train_step(x, y, rows, micro, LR)
+    torch.cuda.synchronize(device)
+    spans, layer._probe = layer._probe, None
+    if rank == 0:
+        work = {}
+        mb = rows // micro
+        for i, p in enumerate(layer.layer_params):
+            k, n = p["weights"].shape
+            is_out = (i == len(layer.layer_params) - 1) and layer.is_output
+            work[f"forward L{i + 1} {k}->{n}"] = (2.0 * mb * k * n, mb * k * 2 + k * n * 2 + mb * n * (4 if is_out else 2))
+            work[f"dX L{i + 1} {n}->{k}"] = (2.0 * mb * k * n, mb * n * 2 + k * n * 2 + 2 * mb * k * 2)
+            work[f"dW+SGD L{i + 1} {k}x{n}"] = (2.0 * rows * k * n, rows * k * 2 + rows * n * 2 + 2 * k * n * 4 + k * n * 2)
+        work[f"softmax-CE N={dims[-1]}"] = (5.0 * mb * dims[-1], mb * dims[-1] * 6 + mb * 8)
+        acc = {}
+        for name, e0, e1 in spans:
+            acc.setdefault(name, []).append(e0.elapsed_time(e1))
+        ks = []
+        for name, ts in acc.items():
+            t = max(1e-6, float(np.mean(ts)))
+            fl, by = work.get(name, (0.0, 0.0))
+            ks.append({"kernel": name, "ms": t, "launches": len(ts) // 2, "tflops": fl / t / 1e9, "gbs": by / t / 1e6,
+                       "flops": fl, "bytes": by,
+                       "how": "CUDA events around the entry point on its launch stream inside pipeline steps (in situ)"})
+        ent["roofline"] = roofline_of(ks, dtype, peaks, workload, in_step=True)
+        ent["kernels"] = _compact(ks)
+    # ---- e2e: HOST batches through PipelineStage.fit_stream (H2D of the batch on the first stage, micro-batch by
+    # micro-batch under the previous step; labels H2D and loss D2H on the last stage) ----
+    try:
+        hx, hy = [None, None], [None, None]
+        if first:  # two pinned host batches (filled from the device batch: host-side RNG of 1 Gi values is slow)
+            hx = [torch.empty((rows, dims[0]), dtype=torch.bfloat16, pin_memory=True) for _ in range(2)]
+            hx[0].copy_(x)
+            hx[1].copy_(x.flip(0))
+        if last:
+            hy = [torch.empty((rows,), dtype=torch.int32, pin_memory=True) for _ in range(2)]
+            hy[0].copy_(y)
+            hy[1].copy_(y.flip(0))
+        torch.cuda.synchronize(device)
+        stage.fit_stream([(hx[i & 1], hy[i & 1]) for i in range(2)], rows, micro, LR)  # untimed: slots, pinned pages
+
+        def e2e_run(_i):
+            losses = stage.fit_stream([(hx[i & 1], hy[i & 1]) for i in range(e2e_steps)], rows, micro, LR)
+            assert not last or (len(losses) == e2e_steps and all(np.isfinite(losses)))
+        e2e_ms = max_over_ranks(timed(e2e_run, 1, 0, device, barrier))
+        ent["e2e"] = {"value": rows * e2e_steps / (e2e_ms / 1e3), "unit": "samples/s",
+                      "h2d_bytes_per_step": rows * dims[0] * 2 + rows * 4, "d2h_bytes_per_step": 4, "steps": e2e_steps,
+                      "api": "PipelineStage.fit_stream (pinned host batch in the compute dtype -> H2D per micro-batch on a "
+                             "copy stream, overlapped with the previous step -> pipeline step -> loss D2H)"}
+        del hx, hy
+    except Exception as e:  # noqa: BLE001
+        ent["e2e"] = {"error": repr(e)[:300]}
+    del stage, layer, x, y
+    torch.cuda.empty_cache()
+    return ent
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS))
     ap.add_argument("--dtype", default=None, choices=["f32", "bf16"])
-    ap.add_argument("--no-extra", action="store_true", help="skip the pipeline/wide sub-benchmarks and cpu_baseline")
+    ap.add_argument("--no-extra", action="store_true", help="headline workload only: no extras, no cpu_baseline")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work for cpu_baseline")
     args = ap.parse_args()
 
@@ -465,10 +703,8 @@ def main():
     device = torch.device("cuda", local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        # lazy communicator init (no device_id): each send/recv pair gets its own communicator and
-        # stream, so stage-boundary transfers do not serialise behind each other
         import datetime
-        dist.init_process_group("nccl", timeout=datetime.timedelta(seconds=240))
+        dist.init_process_group("nccl", timeout=datetime.timedelta(seconds=600))
     barrier = (lambda: dist.barrier(device_ids=[local])) if world > 1 else None
 
     def max_over_ranks(ms):
@@ -480,114 +716,64 @@ def main():
 
     peaks = load_peaks()
     steps, warmup = max(1, args.steps), max(3, args.warmup)
-    workload = args.workload or "mnist4096"
-    is_pipe_workload = workload.startswith("wide") and world > 1
+    workload = args.workload or DEFAULT_WORKLOAD
+    is_wide = workload.startswith("wide")
 
     sampler = ClockSampler(local)
     sampler.start()
-    if is_pipe_workload:
-        pr = bench_pipeline(workload, steps, warmup, device, rank, world, barrier)
-        res = {"rows": pr["rows"], "dims": pr["dims"], "dtype": "bf16", "ms_total": pr["ms_total"],
-               "launches_per_step": pr["launches_per_step"], "cuda_graph": False}
-        replicas = 1
+    if is_wide:
+        head = wide_entry(workload, steps, warmup, device, rank, world, barrier, max_over_ranks, peaks)
+        if "skipped" in head:
+            raise SystemExit(f"bench.py: {head['skipped']}")
     else:
-        res, _tr, _xs, _ys = bench_single(workload, args.dtype, steps, warmup, device, barrier)
-        res["e2e_ms_total"] = max_over_ranks(res["e2e_ms_total"])
-        if rank == 0:
-            res["kernels"] = kernel_roofline(_tr, _xs, _ys, res["dtype"], steps, device, res["cuda_graph"])
-        del _tr, _xs, _ys
-        replicas = world
-    ms_total = max_over_ranks(res["ms_total"])
+        head = small_net_entry(workload, args.dtype, steps, warmup, device, rank, world, barrier, max_over_ranks, peaks)
     clocks = sampler.stop()
     torch.cuda.empty_cache()
-    if world > 1:
-        dist.barrier(device_ids=[local])
 
-    dims, rows = res["dims"], res["rows"]
-    value = replicas * rows * steps / (ms_total / 1e3)
+    dims = WORKLOADS[workload][0]
     fps = flops_per_sample(dims)
     line = {
-        "metric": "train samples/sec (fwd+bwd+SGD)", "value": value, "unit": "samples/s", "n_gpus": world,
-        "steps": steps, "warmup": warmup, "ms_per_step": ms_total / steps, "higher_is_better": True,
-        "scaling": "strong" if is_pipe_workload else "weak", "vs_baseline": None, "dtype": res["dtype"],
-        "data": "synthetic",
-        "config": {"workload": workload, "dims": dims, "rows_per_step_per_gpu": rows,
-                   "parallelism": (f"pipeline{world}" if is_pipe_workload else
-                                   ("single" if world == 1 else f"replicas{world} (net too small to pipeline)")),
-                   "l2": f"inputs rotate over {res.get('pool_batches', 1)} distinct resident batches "
-                         f"({res.get('pool_bytes', 0) / 2**20:.0f} MiB > 126 MiB L2)",
-                   "cuda_graph": res["cuda_graph"], "lr": 0.01},
+        "metric": "train samples/sec (fwd+bwd+SGD)", "value": head["value"], "unit": "samples/s", "n_gpus": world,
+        "steps": steps, "warmup": warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True,
+        "scaling": head["scaling"], "vs_baseline": None, "dtype": head["dtype"], "data": "synthetic",
+        "config": line_config(workload, world),
         "clocks": clocks,
-        "gpu_launches": int(res["launches_per_step"]) * steps,
+        "gpu_launches": int(head["launches_per_step"]) * steps,
         "model_flops_per_sample": fps,
-        "tflops": value * fps / 1e12,
-        "tensor_frac_of_measured_burst": value * fps / 1e12 / (world * peaks["bf16_tflops"]),
-        # activation bytes per sample x samples/s over the measured HBM peak
-        "step_hbm_bytes_per_sample": bytes_per_sample(dims, 4 if res["dtype"] == "f32" else 2),
-        "step_hbm_frac_of_measured": value * bytes_per_sample(dims, 4 if res["dtype"] == "f32" else 2) /
-                                     (world * peaks["hbm_gbs"] * 1e9),
+        "tflops": head["value"] * fps / 1e12,
+        "tensor_frac_of_measured_burst": head["value"] * fps / 1e12 / (world * peaks["bf16_tflops"]),
+        "tensor_frac_of_measured_sustained": head["value"] * fps / 1e12 / (world * peaks["bf16_tflops_sustained"]),
         "peaks": peaks,
     }
-    if "e2e_ms_total" in res:
-        e2e_v = replicas * rows * res["e2e_steps"] / (res["e2e_ms_total"] / 1e3)
-        line["e2e"] = {"value": e2e_v, "unit": "samples/s", "h2d_bytes_per_step": res["h2d"],
-                       "d2h_bytes_per_step": res["d2h"], "steps": res["e2e_steps"],
-                       "api": res["e2e_api"]}
-    if "kernels" in res:
-        ks = res["kernels"]
-        dom = max(ks, key=lambda r: r["ms"])
-        elt_bound = "tensor" if (res["dtype"] == "bf16" and dom["flops"] / dom["bytes"] > 255) else "hbm"
-        if elt_bound == "tensor":
-            roof = {"bound": "tensor", "achieved": dom["tflops"], "peak": peaks["bf16_tflops"], "unit": "TFLOP/s",
-                    "frac": dom["tflops"] / peaks["bf16_tflops"]}
-        else:
-            roof = {"bound": "hbm", "achieved": dom["gbs"], "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": dom["gbs"] / peaks["hbm_gbs"]}
-        traffic = None
-        try:
-            with open(os.path.join(REPO, "profiles", "traffic.json")) as f:
-                traffic = json.load(f).get(workload, {}).get(dom["kernel"])
-        except Exception:  # noqa: BLE001
-            pass
-        roof.update({"traffic": traffic, "algorithmic_bytes": dom["bytes"], "kernel": dom["kernel"], "ms_per_launch": dom["ms"],
-                     "peak_source": peaks["source"], "kernel_tflops": dom["tflops"],
-                     "step_share": dom["ms"] / sum(r["ms"] for r in ks),
-                     "timing": dom["how"]})
-        line["roofline"] = roof
-        line["kernels"] = [{k: (round(v, 6) if isinstance(v, float) else v) for k, v in r.items()
-                            if k in ("kernel", "ms", "tflops", "gbs")} for r in ks]
+    for k in ("e2e", "roofline", "kernels", "stages", "transport", "schedule", "bubble_bound", "loss_first_steps",
+              "loss_first_steps_hex", "weights_checksum", "weights_checksum_per_layer", "checksum_of", "cuda_graph", "l2",
+              "step_hbm_bytes_per_sample", "step_hbm_frac_of_measured"):
+        if k in head:
+            line[k] = head[k]
 
-    # ---- extras: the wide nets (tensor-core roofline + pipeline), and the CPU baseline ----
-    if not args.no_extra and not is_pipe_workload:
-        pipes = []
-        for wl in ("wide4x8192", "wide8x16384"):
-            n_layers = len(WORKLOADS[wl][1])
-            if world > n_layers:
+    # ---- extras: the other configs, each a full report (value, e2e, roofline); the CPU baseline ----
+    if not args.no_extra:
+        extras = []
+        es, ew = max(steps, 20), max(warmup, 5)
+        for wl in ("mnist4096", "narrow65536", "wide4x8192", "wide8x16384"):
+            if wl == workload:
                 continue
             try:
-                psteps = max(2, min(steps, 6 if wl == "wide8x16384" else 12))
-                pr = bench_pipeline(wl, psteps, 3, device, rank, world, barrier)
-                pms = max_over_ranks(pr["ms_total"])
-                v = pr["rows"] * psteps / (pms / 1e3)
-                f = flops_per_sample(pr["dims"])
-                pipes.append({"workload": wl, "stages": world, "micro_batches": pr["micro_batches"],
-                              "sm_reserve": pr["sm_reserve"], "transport": pr["transport"],
-                              "rows_per_step": pr["rows"], "steps": psteps, "ms_per_step": pms / psteps,
-                              "value": v, "unit": "samples/s", "scaling": "strong", "tflops_total": v * f / 1e12,
-                              "tensor_frac_of_measured_burst": v * f / 1e12 / (world * peaks["bf16_tflops"]),
-                              "tensor_frac_of_measured_sustained":
-                                  v * f / 1e12 / (world * peaks["bf16_tflops_sustained"]),
-                              "bubble_bound": (3 * pr["micro_batches"]) /
-                                              (3 * pr["micro_batches"] + 2 * (world - 1))})
+                if wl.startswith("wide"):
+                    if wl == "wide8x16384" or world > 4:
+                        continue  # the 16384-wide net is the default headline; 4 layers do not split over 8 GPUs
+                    extras.append(wide_entry(wl, min(es, 12), 3, device, rank, world, barrier, max_over_ranks, peaks))
+                elif world == 1:  # the small nets do not pipeline: measured on one GPU only
+                    extras.append(small_net_entry(wl, None, max(es, 50), ew, device, rank, world, barrier,
+                                                  max_over_ranks, peaks))
             except Exception as e:  # noqa: BLE001
-                pipes.append({"workload": wl, "error": repr(e)[:300]})
+                extras.append({"workload": wl, "error": repr(e)[:300]})
             torch.cuda.empty_cache()
-        line["pipeline"] = pipes
-    if rank == 0 and not args.no_extra and world == 1:
-        v, desc, ms, n = cpu_train_samples_per_s(workload, args.cpu_budget, warmup=1,
-                                                 rows_cap={"narrow65536": 8192, "wide4x8192": 64,
-                                                           "wide8x16384": 16}.get(workload))
-        line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cpu_threads(), "kind": "port", "sample": desc}
+        line["extras"] = extras
+        if rank == 0 and world == 1:
+            v, desc, ms, n = cpu_train_samples_per_s(workload, args.cpu_budget, warmup=1)
+            line["cpu_baseline"] = {"value": v, "unit": "samples/s", "cores": cpu_threads(), "kind": "port",
+                                    "sample": desc}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -63,7 +63,11 @@ class PipelineStage:
     GEMM epilogues write into them directly over NVLink; arrival is signalled with 4-byte flags and
     stream memory waits -- no NCCL kernel, no copy and no host synchronisation in the data path."""
 
-    def __init__(self, layer, rank: int, world_size: int, group=None, transport: str = "nccl"):
+    def __init__(self, layer, rank: int, world_size: int, group=None, transport: str = "nccl",
+                 schedule: str = "gpipe"):
+        if schedule not in ("gpipe", "zb"):
+            raise ValueError(f"schedule must be 'gpipe' or 'zb', got {schedule!r}")
+        self.schedule = schedule
         self.layer = layer
         self.rank = rank
         self.world = world_size
@@ -129,7 +133,7 @@ class PipelineStage:
         _lib.check(_lib.lib.ddnn_flag_wait(self._peer["flags"].data_ptr() + 4 * idx, value,
                                            torch.cuda.current_stream(self.layer.device).cuda_stream))
 
-    def _train_step_peer(self, x, labels, rows: int, micro_batches: int, lr: float):
+    def _train_step_peer(self, x, labels, rows: int, micro_batches: int, lr: float, ready=None):
         L = self.layer
         L.begin_batch(rows)
         slices = micro_batch_slices(rows, micro_batches)
@@ -143,6 +147,8 @@ class PipelineStage:
             in_place = self.first and self._adopt_input(x)
             for m, (r0, r1) in enumerate(slices):
                 n = r1 - r0
+                if ready is not None:
+                    torch.cuda.current_stream(L.device).wait_event(ready[m])  # host copy of these rows has landed
                 if not self.first:
                     self._flag_wait(m, t)                    # micro-batch m of step t has landed here
                 if not self.last and m == 0 and t > 1:
@@ -186,18 +192,22 @@ class PipelineStage:
         dist.recv(t, src=src, group=self.group)
 
     def train_step(self, x: Optional[torch.Tensor], labels: Optional[torch.Tensor], rows: int,
-                   micro_batches: int, lr: float):
+                   micro_batches: int, lr: float, ready=None):
         """One GPipe step over ``rows`` examples.  ``x`` is needed on the first stage,
-        ``labels`` (int32) on the last.  Returns the loss tensor on the last stage, else None."""
+        ``labels`` (int32) on the last.  Returns the loss tensor on the last stage, else None.
+        ``ready`` (first stage, optional): one CUDA event per micro-batch that the forward of that
+        micro-batch waits for -- the host-to-device copy of its rows (``fit_stream``)."""
         if self.transport == "peer":
-            return self._train_step_peer(x, labels, rows, micro_batches, lr)
+            return self._train_step_peer(x, labels, rows, micro_batches, lr, ready)
         L = self.layer
         L.begin_batch(rows)
         slices = micro_batch_slices(rows, micro_batches)
         # ---- forward: fill ----
         in_place = self.first and self._adopt_input(x)
-        for (r0, r1) in slices:
+        for m, (r0, r1) in enumerate(slices):
             n = r1 - r0
+            if ready is not None:
+                torch.cuda.current_stream(L.device).wait_event(ready[m])
             if self.first:
                 out = L.forward_train(None, r0, n) if in_place else L.forward_train(x[r0:r1], r0)
             else:
@@ -219,6 +229,73 @@ class PipelineStage:
         # ---- update: full-batch dW GEMMs with fused SGD ----
         L.step(lr, rows)
         return loss
+
+    # ------------------------------------------------------------------ host-facing loop
+    def fit_stream(self, batches, rows: int, micro_batches: int, lr: float) -> List[float]:
+        """Trains on a sequence of HOST batches, one pipeline step each, in order (the batch order of
+        run_grpc_inference.py:198-205).  ``batches[i] = (x_host, y_host)``: ``x_host`` (rows, in) pinned, in
+        the compute dtype, is read on the FIRST stage only (other stages may pass None); ``y_host`` (rows,)
+        pinned int32 on the LAST stage only.  Every stage calls this with the same number of batches.
+
+        First stage: two device slots; a copy stream moves batch i+1 host-to-device micro-batch by
+        micro-batch while step i computes, the forward of a micro-batch waits only for its own rows, and
+        layer 1 reads the slot in place.  Last stage: labels H2D and the loss D2H of every step are
+        stream-ordered; one synchronisation at the end.  Returns the per-step losses on the last stage
+        ([] elsewhere)."""
+        batches = list(batches)
+        if not batches:
+            return []
+        L = self.layer
+        dev = L.device
+        L.begin_batch(rows)
+        slices = micro_batch_slices(rows, micro_batches)
+        key = (rows, len(slices), L._gen)
+        st = getattr(self, "_host", None)
+        if st is None or st["key"] != key:
+            st = {"key": key, "copy": torch.cuda.Stream(device=dev)}
+            if self.first:
+                st["slots"] = [torch.empty((rows, L.expected_input_dim), dtype=L.wire_dtype, device=dev)
+                               for _ in range(2)]
+                st["ready"] = [[torch.cuda.Event() for _ in slices] for _ in range(2)]
+                st["done"] = [torch.cuda.Event() for _ in range(2)]
+            if self.last:
+                st["labels"] = [torch.empty((rows,), dtype=torch.int32, device=dev) for _ in range(2)]
+                st["ldone"] = [torch.cuda.Event() for _ in range(2)]
+                st["lready"] = [torch.cuda.Event() for _ in range(2)]
+            self._host = st
+        cur = torch.cuda.current_stream(dev)
+        for k in ("done", "ldone"):
+            for ev in st.get(k, []):
+                ev.record(cur)
+        losses_host = torch.empty((len(batches),), dtype=torch.float32).pin_memory() if self.last else None
+        for i, (hx, hy) in enumerate(batches):
+            s_ = i & 1
+            x = y = ready = None
+            with torch.cuda.stream(st["copy"]):
+                if self.first:
+                    if hx.dtype != L.wire_dtype or tuple(hx.shape) != (rows, L.expected_input_dim):
+                        raise ValueError(f"fit_stream: host batch must be ({rows}, {L.expected_input_dim}) "
+                                         f"{L.wire_dtype}, got {tuple(hx.shape)} {hx.dtype}")
+                    x, ready = st["slots"][s_], st["ready"][s_]
+                    st["copy"].wait_event(st["done"][s_])      # slot free: step i-2 (its last reader dW_1) is done
+                    for m, (r0, r1) in enumerate(slices):
+                        x[r0:r1].copy_(hx[r0:r1], non_blocking=True)
+                        ready[m].record(st["copy"])
+                if self.last:
+                    y = st["labels"][s_]
+                    st["copy"].wait_event(st["ldone"][s_])
+                    y.copy_(hy, non_blocking=True)
+                    st["lready"][s_].record(st["copy"])
+            if self.last:
+                cur.wait_event(st["lready"][s_])
+            loss = self.train_step(x, y, rows, micro_batches, lr, ready=ready)
+            if self.first:
+                st["done"][s_].record(cur)
+            if self.last:
+                st["ldone"][s_].record(cur)
+                losses_host[i:i + 1].copy_(loss, non_blocking=True)
+        torch.cuda.synchronize(dev)
+        return losses_host.tolist() if self.last else []
 
     def infer(self, x: Optional[torch.Tensor], rows: int, micro_batches: int) -> Optional[torch.Tensor]:
         """Forward-only relay (what the reference chain does): the last stage returns the

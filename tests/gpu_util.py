@@ -26,3 +26,13 @@ F32_TOL = 1e-5
 # the float64 oracle (normalised max error), weight gradients within 3e-2
 BF16_ACT_TOL = 2e-2
 BF16_GRAD_TOL = 3e-2
+
+
+def elementwise_ok(got, ref, rtol: float, atol: float) -> bool:
+    """Elementwise check beside the normalised-max one: |got - ref| <= rtol * |ref| + atol for EVERY element, so
+    an element far below the tensor's maximum cannot hide a large relative error behind it.  ``atol`` is stated
+    by the caller in the units of the tensor (it covers elements that cancel to ~0)."""
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape, (got.shape, ref.shape)
+    return bool(np.all(np.abs(got - ref) <= rtol * np.abs(ref) + atol))
