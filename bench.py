@@ -163,7 +163,11 @@ DEFAULT_WORKLOAD = "wide8x16384"
 LR = 0.01
 # rows of one CPU step (a bounded sample of the workload's batch): the oracle's float64 GEMMs are compute-bound
 # from ~100 rows on, and 20 + 5 steps must end within minutes on the host cores
-CPU_ROWS = {"mnist4096": 4096, "narrow65536": 8192, "wide4x8192": 256, "wide8x16384": 128}
+CPU_ROWS = {"mnist4096": 4096, "narrow65536": 8192, "wide4x8192": 256, "wide8x16384": 256}
+# ... and layers: every layer of a wide net has the same shape, and a float64 step over all eight 16384 x 16384
+# layers spends 12 s of which most is weight-sized memory passes, so the CPU arm times the LAST two (dX, dW + SGD of
+# a hidden layer, the softmax-CE output layer) and scales samples/s by their share of the step's FLOPs
+CPU_LAYERS = {"wide8x16384": 2}
 
 
 def line_config(workload: str, world: int):
@@ -189,28 +193,25 @@ def cpu_train_samples_per_s(workload: str, budget_s: float, steps=None, warmup=1
     from ddnn_b200.config import make_params, synthetic_batch
     dims, acts, rows, _, _ = WORKLOADS[workload]
     rows = min(rows, rows_cap or CPU_ROWS[workload])
-    note = ""
-    try:  # float64 weights + gradients + the updated copy of the 16384-wide net: ~3 x 17 GB
-        import psutil
-        need = 3.2 * 8 * sum(k * n for k, n in zip(dims[:-1], dims[1:]))
-        if need > 0.6 * psutil.virtual_memory().available:
-            keep = max(2, int(len(acts) * 0.6 * psutil.virtual_memory().available / need))
-            note = f"; host RAM holds {keep} of the {len(acts)} layers in float64: timed on the last {keep}, " \
-                   f"samples/s scaled by their share of the step's FLOPs"
-            scale = flops_per_sample(dims[-(keep + 1):]) / flops_per_sample(dims)
-            dims, acts = dims[-(keep + 1):], acts[-keep:]
-        else:
-            scale = 1.0
-    except Exception:  # noqa: BLE001
-        scale = 1.0
+    note, scale = "", 1.0
+    keep = CPU_LAYERS.get(workload)
+    if keep and keep < len(acts):
+        # the sub-net's first layer also computes dX here (in the full net only layer 1 skips it)
+        sub = sum(6 * k * n for k, n in zip(dims[-(keep + 1):-1], dims[-keep:]))
+        scale = sub / flops_per_sample(dims)
+        note = f"; timed on the last {keep} of the {len(acts)} equal layers (incl. their dX), samples/s scaled by " \
+               f"their share {scale:.4f} of the step's FLOPs"
+        dims, acts = dims[-(keep + 1):], acts[-keep:]
     params = make_params(dims, acts, seed=1)
     x, y = synthetic_batch(rows, dims[0], dims[-1], seed=0)
-    for _ in range(max(0, warmup)):
+    def one_step():  # oracle.backward also computes dX of the first layer it is given
         oracle.train_step(params, x, y, LR)
+    for _ in range(max(0, warmup)):
+        one_step()
     t0 = time.perf_counter()
     n = 0
     while True:
-        oracle.train_step(params, x, y, LR)
+        one_step()
         n += 1
         el = time.perf_counter() - t0
         if (steps is not None and n >= steps) or (steps is None and el >= budget_s):

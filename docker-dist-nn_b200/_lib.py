@@ -22,6 +22,14 @@ STATIC_SCRATCH_BYTES = 8 * 1024 * 1024  # DDNN_STATIC_SCRATCH_BYTES
 
 _vp, _i64, _i32, _f32, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_float, C.c_size_t
 
+
+
+class Signals(C.Structure):
+    """``ddnn_signals`` (include/ddnn.h): flag wait / flag publish folded into a GEMM kernel."""
+    _fields_ = [("wait_flag", C.c_void_p), ("wait_value", C.c_int32), ("done_flag", C.c_void_p),
+                ("done_value", C.c_int32), ("counter", C.c_void_p)]
+
+
 SYMBOLS = {
     "ddnn_version": (C.c_int, []),
     "ddnn_last_error": (C.c_char_p, []),
@@ -32,6 +40,10 @@ SYMBOLS = {
     "ddnn_set_cta_pairs": (C.c_int, [_i32]),
     "ddnn_set_pdl": (C.c_int, [_i32]),
     "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
+    "ddnn_dense_forward_signalled": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32,
+                                               C.POINTER(Signals), _vp]),
+    "ddnn_dense_backward_dx_signalled": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32,
+                                                   C.POINTER(Signals), _vp]),
     "ddnn_softmax_rows": (C.c_int, [_vp, _vp, _i64, _i64, _vp]),
     "ddnn_activate": (C.c_int, [_vp, _vp, _i64, _i64, _i32, _vp]),
     "ddnn_softmax_ce": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _f32, _i32, _i32, _vp]),

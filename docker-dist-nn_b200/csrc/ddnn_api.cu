@@ -139,9 +139,24 @@ int ddnn_set_sm_reserve(int sms) {
 
 int64_t ddnn_launch_count(void) { return (int64_t)g_launches.load(); }
 
+static int check_signals(const char* fn, const ddnn_signals* sig) {
+  if (sig && sig->done_flag && !sig->counter) {
+    set_error("%s: ddnn_signals.done_flag needs a counter", fn);
+    return DDNN_ERR_ARG;
+  }
+  return DDNN_OK;
+}
+
 int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K, int64_t N,
                        int act, int dtype, int out_dtype, void* stream) {
+  return ddnn_dense_forward_signalled(X, W, bias, A, B, K, N, act, dtype, out_dtype, nullptr, stream);
+}
+
+int ddnn_dense_forward_signalled(const void* X, const void* W, const float* bias, void* A, int64_t B, int64_t K,
+                                 int64_t N, int act, int dtype, int out_dtype, const ddnn_signals* sig, void* stream) {
   int rc = check_dims("ddnn_dense_forward", B, K, N);
+  if (rc) return rc;
+  if ((rc = check_signals("ddnn_dense_forward_signalled", sig))) return rc;
   if (rc) return rc;
   if (B == 0) return DDNN_OK;
   if (!X || !W || !bias || !A) {
@@ -158,16 +173,24 @@ int ddnn_dense_forward(const void* X, const void* W, const float* bias, void* A,
   }
   cudaStream_t st = (cudaStream_t)stream;
   const int gemm_act = act == DDNN_ACT_SOFTMAX ? DDNN_ACT_LINEAR : act;
+  const bool umma = !use_skinny(K, N) && use_umma(dtype, B, K, N, {X, W, A});
+  // the tcgen05 kernels take the signals themselves (a softmax pass after the GEMM would run past done_flag);
+  // every other path brackets the plain launch with the stream-ordered flag operations
+  const bool in_kernel = sig && umma && act != DDNN_ACT_SOFTMAX;
+  if (sig && !in_kernel && sig->wait_flag && (rc = ddnn_flag_wait(sig->wait_flag, sig->wait_value, stream))) return rc;
   if (use_skinny(K, N))
     rc = skinny_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
-  else if (use_umma(dtype, B, K, N, {X, W, A}))
-    rc = umma_forward((const bf16*)X, (const bf16*)W, bias, A, B, K, N, gemm_act, out_dtype, st);
+  else if (umma)
+    rc = umma_forward((const bf16*)X, (const bf16*)W, bias, A, B, K, N, gemm_act, out_dtype, st,
+                      in_kernel ? sig : nullptr);
   else if (out_dtype == DDNN_F32 && use_tf32(dtype, B, K, N, K, {X, W, A, bias}))
     rc = tf32_forward((const float*)X, (const float*)W, bias, (float*)A, B, K, N, gemm_act, st);
   else
     rc = simt_forward(X, W, bias, A, B, K, N, gemm_act, dtype, out_dtype, st);
   if (rc) return rc;
   if (act == DDNN_ACT_SOFTMAX) rc = softmax_rows((const float*)A, (float*)A, B, N, st);
+  if (rc) return rc;
+  if (sig && !in_kernel && sig->done_flag) rc = ddnn_flag_write(sig->done_flag, sig->done_value, stream);
   return rc;
 }
 
@@ -215,8 +238,15 @@ int ddnn_softmax_ce(const float* Z, const int32_t* labels, float* P, void* dZ, f
 
 int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, void* dZprev, int64_t B, int64_t K,
                            int64_t N, int act_prev, int dtype, void* stream) {
+  return ddnn_dense_backward_dx_signalled(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, nullptr, stream);
+}
+
+int ddnn_dense_backward_dx_signalled(const void* dZ, const void* W, const void* Aprev, void* dZprev, int64_t B,
+                                     int64_t K, int64_t N, int act_prev, int dtype, const ddnn_signals* sig,
+                                     void* stream) {
   int rc = check_dims("ddnn_dense_backward_dx", B, K, N);
   if (rc) return rc;
+  if ((rc = check_signals("ddnn_dense_backward_dx_signalled", sig))) return rc;
   if (B == 0) return DDNN_OK;
   if (!dZ || !W || !dZprev) {
     set_error("ddnn_dense_backward_dx: null pointer");
@@ -235,13 +265,19 @@ int ddnn_dense_backward_dx(const void* dZ, const void* W, const void* Aprev, voi
     return DDNN_ERR_ARG;
   }
   cudaStream_t st = (cudaStream_t)stream;
-  if (use_skinny(K, N)) return skinny_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
-  if (use_umma(dtype, B, K, N, {dZ, W, Aprev, dZprev}))
-    return umma_dx((const bf16*)dZ, (const bf16*)W, (const bf16*)Aprev, (bf16*)dZprev, B, K, N, act_prev, st);
-  // the dX GEMM's output is (B x K) and its reduction runs over N
-  if (use_tf32(dtype, B, N, K, N, {dZ, W, Aprev, dZprev}))
-    return tf32_dx((const float*)dZ, (const float*)W, (const float*)Aprev, (float*)dZprev, B, K, N, act_prev, st);
-  return simt_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
+  const bool umma = !use_skinny(K, N) && use_umma(dtype, B, K, N, {dZ, W, Aprev, dZprev});
+  if (umma)  // signals (if any) handled inside the kernel
+    return umma_dx((const bf16*)dZ, (const bf16*)W, (const bf16*)Aprev, (bf16*)dZprev, B, K, N, act_prev, st, sig);
+  if (sig && sig->wait_flag && (rc = ddnn_flag_wait(sig->wait_flag, sig->wait_value, stream))) return rc;
+  if (use_skinny(K, N))
+    rc = skinny_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
+  else if (use_tf32(dtype, B, N, K, N, {dZ, W, Aprev, dZprev}))  // output (B x K), reduction over N
+    rc = tf32_dx((const float*)dZ, (const float*)W, (const float*)Aprev, (float*)dZprev, B, K, N, act_prev, st);
+  else
+    rc = simt_dx(dZ, W, Aprev, dZprev, B, K, N, act_prev, dtype, st);
+  if (rc) return rc;
+  if (sig && sig->done_flag) rc = ddnn_flag_write(sig->done_flag, sig->done_value, stream);
+  return rc;
 }
 
 static size_t np_of(int64_t N) { return (size_t)((N + 3) & ~(int64_t)3); }

@@ -62,10 +62,11 @@ int cast_bf16_f32(const bf16* in, float* out, int64_t n, cudaStream_t st);
 bool umma_shape_ok(int64_t B, int64_t K, int64_t N);
 void umma_set_sm_reserve(int sms);
 void umma_set_pair(int on);  // 1: CTA-pair (cta_group::2) kernel where it applies (default)
+// sig (optional): pipeline signalling folded into the kernel, see ddnn_signals in include/ddnn.h
 int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64_t B, int64_t K,
-                 int64_t N, int act, int out_dtype, cudaStream_t st);
+                 int64_t N, int act, int out_dtype, cudaStream_t st, const ddnn_signals* sig = nullptr);
 int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int64_t B, int64_t K,
-            int64_t N, int act_prev, cudaStream_t st);
+            int64_t N, int act_prev, cudaStream_t st, const ddnn_signals* sig = nullptr);
 // Split-K plan for dW on tcgen05; splits == 1 means the SGD/store epilogue is fused.
 int umma_dw_splits(int64_t B, int64_t K, int64_t N);
 // db_part/db_fused (optional): when the split-K plan puts one tile on every CTA the kernel also writes the

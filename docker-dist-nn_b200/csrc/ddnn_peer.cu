@@ -21,11 +21,6 @@ __global__ void flag_write_kernel(volatile int32_t* flag, int32_t value) {
   *flag = value;
 }
 
-__global__ void flag_spin_kernel(const volatile int32_t* flag, int32_t value) {
-  while (*flag < value) __nanosleep(200);
-  __threadfence_system();
-}
-
 typedef CUresult (*WaitValue32Fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
 typedef CUresult (*AddrRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
 
@@ -110,14 +105,17 @@ int ddnn_flag_wait(const int32_t* flag, int32_t value, void* stream) {
     return DDNN_ERR_ARG;
   }
   static WaitValue32Fn wait32 = (WaitValue32Fn)driver_fn("cuStreamWaitValue32");
-  if (wait32) {
-    CUresult r = wait32((CUstream)stream, (CUdeviceptr)flag, (cuuint32_t)value, CU_STREAM_WAIT_VALUE_GEQ);
-    if (r == CUDA_SUCCESS) return DDNN_OK;
+  if (!wait32) {
+    set_error("ddnn_flag_wait: this driver has no cuStreamWaitValue32 (stream memory operations)");
+    return DDNN_ERR_UNSUPPORTED;
   }
-  // stream memory operations unavailable: a one-thread kernel polls the (local) flag instead
-  flag_spin_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(flag, value);
-  count_launch();
-  DDNN_LAUNCH_CHECK();
+  // A polling kernel would be the alternative, but on one GPU it can deadlock behind the very stream that has
+  // to produce the flag, so a driver that refuses the memory operation is reported instead of worked around.
+  CUresult r = wait32((CUstream)stream, (CUdeviceptr)flag, (cuuint32_t)value, CU_STREAM_WAIT_VALUE_GEQ);
+  if (r != CUDA_SUCCESS) {
+    set_error("ddnn_flag_wait: cuStreamWaitValue32 failed (%d)", (int)r);
+    return DDNN_ERR_CUDA;
+  }
   return DDNN_OK;
 }
 

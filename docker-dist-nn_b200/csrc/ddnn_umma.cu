@@ -42,7 +42,43 @@ struct UmmaParams {
   uint64_t hint_a, hint_b;  // L2 eviction-priority policies of the A / B operand loads (CTA-pair kernel)
   float* db_part;  // dW split-K (EPI_STORE, one tile per CTA): column sums of the B operand, [split][db_np]
   int db_np;
+  // Pipeline signalling folded into the GEMM (ddnn_signals): the TMA producer polls *wait_flag >= wait_value
+  // before its first operand load; the last CTA to finish stores done_value to *done_flag (a local or
+  // peer-mapped flag) after a system-scope fence.  Null pointers switch either half off.
+  const int32_t* wait_flag;
+  int32_t wait_value;
+  int32_t* done_flag;
+  int32_t done_value;
+  unsigned int* done_counter;
 };
+
+// The operands behind `flag` were written by another GPU (peer stores over NVLink) or another stream: poll with
+// acquire semantics at system scope, then order the acquire (generic proxy) before the TMA reads (async proxy).
+__device__ __forceinline__ void wait_operands(const UmmaParams& p) {
+  if (p.wait_flag == nullptr) return;
+  int32_t v;
+  while (true) {
+    asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(p.wait_flag) : "memory");
+    if (v >= p.wait_value) break;
+    __nanosleep(64);
+  }
+  asm volatile("fence.proxy.async.global;" ::: "memory");
+}
+
+// Called by ONE thread per CTA after the CTA-wide (cluster-wide) barrier that follows the epilogue: the barrier
+// makes every epilogue store of the CTA observed by this thread, the system-scope fence + counter increment
+// releases them, and the CTA that sees the full count publishes the flag -- also to a flag in a peer GPU's
+// memory -- so the consumer's wait on the flag orders it after every tile of this GEMM.
+__device__ __forceinline__ void publish_done(const UmmaParams& p) {
+  if (p.done_flag == nullptr) return;
+  __threadfence_system();
+  const unsigned int prev = atomicAdd(p.done_counter, 1u);
+  if (prev == gridDim.x - 1) {
+    atomicExch(p.done_counter, 0u);  // the next GEMM of the stream counts from zero (it increments after we completed)
+    __threadfence_system();
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(p.done_flag), "r"(p.done_value) : "memory");
+  }
+}
 
 // K-major tile [rows][64] (row = 128 B, 8-row swizzle atoms 1024 B apart): step k by 32 bytes.
 // MN-major tile: 64-element MN atoms, each [64 k][64 mn] (k row = 128 B): 8-k groups 1024 B apart
@@ -290,6 +326,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
+      wait_operands(p);
       uint32_t stage = 0, phase = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const TileCoord t = decode_tile(tile, p);
@@ -395,6 +432,7 @@ umma_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
   }
+  if (threadIdx.x == 0) publish_done(p);
 }
 
 // ===================== CTA-pair kernel: 256 x 256 tile per 2-CTA cluster =====================
@@ -476,6 +514,7 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
   if (warp == 0) {
     // ===================== TMA producer (both CTAs) =====================
     if (lane == 0) {
+      wait_operands(p);
       uint32_t stage = 0, phase = 0;
       for (int tile = pair; tile < total_tiles; tile += num_pairs) {
         const TileCoord t = decode_tile(tile, p);
@@ -564,6 +603,7 @@ umma_pair_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_co
     tc_fence_after();
     tmem_dealloc_pair(tmem_base, C::TMEM_COLS);
   }
+  if (threadIdx.x == 0) publish_done(p);
 }
 
 // ---- host side ------------------------------------------------------------------------
@@ -780,8 +820,17 @@ void umma_set_sm_reserve(int sms) { g_sm_reserve.store(sms < 0 ? 0 : sms); }
 
 bool umma_shape_ok(int64_t B, int64_t K, int64_t N) { return B > 0 && K >= 8 && N >= 8 && K % 8 == 0 && N % 8 == 0; }
 
+static void set_signals(UmmaParams& p, const ddnn_signals* sig) {
+  if (!sig) return;
+  p.wait_flag = sig->wait_flag;
+  p.wait_value = sig->wait_value;
+  p.done_flag = sig->counter ? sig->done_flag : nullptr;
+  p.done_value = sig->done_value;
+  p.done_counter = sig->counter;
+}
+
 int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64_t B, int64_t K, int64_t N, int act,
-                 int out_dtype, cudaStream_t st) {
+                 int out_dtype, cudaStream_t st, const ddnn_signals* sig) {
   const int bn = pick_bn(N);
   CUtensorMap ta, tb;
   int rc = operand_maps(false, X, true, W, B, N, K, bn, &ta, &tb);
@@ -791,6 +840,7 @@ int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64
   p.bias = bias;
   p.act = act;
   p.out = A;
+  set_signals(p, sig);
   if (pair_ok(bn, p)) {
     if (out_dtype == DDNN_BF16) return launch_pair<false, true, EPI_FWD_BF16>(ta, tb, p, st);
     return launch_pair<false, true, EPI_FWD_F32>(ta, tb, p, st);
@@ -800,7 +850,7 @@ int umma_forward(const bf16* X, const bf16* W, const float* bias, void* A, int64
 }
 
 int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int64_t B, int64_t K, int64_t N,
-            int act_prev, cudaStream_t st) {
+            int act_prev, cudaStream_t st, const ddnn_signals* sig) {
   // D[B, K] = dZ[B, N] . W[K, N]^T : GEMM-N = K (layer input width), reduction = N
   const int bn = pick_bn(K);
   UmmaParams p{};
@@ -808,6 +858,7 @@ int umma_dx(const bf16* dZ, const bf16* W, const bf16* Aprev, bf16* dZprev, int6
   p.act = act_prev;
   p.aprev = Aprev;
   p.out = dZprev;
+  set_signals(p, sig);
   const bool pair = pair_ok(bn, p);
   CUtensorMap ta, tb;
   int rc = operand_maps(false, dZ, false, W, B, K, N, bn, &ta, &tb, pair);

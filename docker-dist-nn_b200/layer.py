@@ -63,6 +63,8 @@ class _Span:
 
 
 class Layer:
+    supports_signals = True  # forward_train / backward take wait= / signal= (flags folded into the GEMM kernels)
+
     def __init__(self, dtype: Optional[str] = None, device=None):
         # grpc_node.py:17-58 -- identical environment contract and failure behaviour
         self.container_name = os.environ.get("CONTAINER_NAME", "layer")
@@ -285,13 +287,17 @@ class Layer:
         return self._bufs["a"][-1][row0:row0 + rows]
 
     def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None,
-                      out_target: Optional[torch.Tensor] = None, skip_last: int = 0) -> torch.Tensor:
+                      out_target: Optional[torch.Tensor] = None, skip_last: int = 0,
+                      wait=None, signal=None) -> torch.Tensor:
         """Forward of rows [row0, row0+rows) keeping what backward needs.  ``x`` None means the
         rows are already in ``input_buffer``.  An output node stops at the fp32 logits Z
         (softmax is fused into ``loss_and_grad``).  ``out_target`` (rows, N_last) redirects the
         LAST local layer's output, e.g. to the next stage's input buffer mapped from a peer GPU:
         the GEMM epilogue then stores over NVLink and no local copy of that activation exists
-        (this node never reads its own last output)."""
+        (this node never reads its own last output).  ``wait = (flag_address, value)`` makes the FIRST local
+        layer's kernel wait for that flag before it loads its input rows, ``signal = (flag_address, value,
+        counter_address)`` makes the LAST local layer's kernel publish that flag when its output is complete
+        (``ddnn_signals``): the pipeline's arrival / departure flags without a launch of their own."""
         a = self._bufs["a"]
         if x is not None:
             rows = x.shape[0]
@@ -321,8 +327,13 @@ class Layer:
                 raise ValueError("hidden softmax layers are not supported in training (row Jacobian)")
             k_, n_ = p["weights"].shape
             dst = out_target if (last and out_target is not None) else a[i + 1][row0:row0 + rows]
+            sig = None
+            if (wait is not None and i == 0) or (signal is not None and last):
+                w_, s_ = (wait if i == 0 else None), (signal if last else None)
+                sig = ops.make_signals(w_[0] if w_ else None, w_[1] if w_ else 0, s_[0] if s_ else None,
+                                       s_[1] if s_ else 0, s_[2] if s_ else None)
             with self._span(f"forward L{i + 1} {k_}->{n_}"):
-                ops.dense_forward(self._a(i)[row0:row0 + rows], self._w(i), p["biases"], act, out=dst)
+                ops.dense_forward(self._a(i)[row0:row0 + rows], self._w(i), p["biases"], act, out=dst, signals=sig)
         return out_target if out_target is not None else a[-1][row0:row0 + rows]
 
     def loss_and_grad(self, labels: torch.Tensor, row0: int = 0, denom: Optional[int] = None,
@@ -341,24 +352,34 @@ class Layer:
         return b["loss"]
 
     def backward(self, row0: int = 0, rows: Optional[int] = None, need_input_grad: bool = True,
-                 dx_target: Optional[torch.Tensor] = None) -> Optional[torch.Tensor]:
+                 dx_target: Optional[torch.Tensor] = None, wait=None, signal=None) -> Optional[torch.Tensor]:
         """dX chain for rows [row0, row0+rows): dZ[l-1] = (dZ[l].W_l^T) * f'_{l-1}(A[l]).  Returns
         dZ for the node feeding this one (already multiplied by that node's activation
-        derivative, ``input_activation``) or None when ``need_input_grad`` is False."""
+        derivative, ``input_activation``) or None when ``need_input_grad`` is False.  ``wait`` / ``signal`` as in
+        ``forward_train``: the first dX kernel of the chain (the one that reads the gradient received from
+        downstream) waits, the dX that produces the upstream gradient publishes."""
         rows = self._rows - row0 if rows is None else rows
         b = self._bufs
         sl = slice(row0, row0 + rows)
-        for i in range(len(self.layer_params) - 1, 0, -1):
+        top = len(self.layer_params) - 1
+        for i in range(top, 0, -1):
             k_, n_ = self.layer_params[i]["weights"].shape
+            sig = ops.make_signals(wait[0], wait[1]) if (wait is not None and i == top) else None
             with self._span(f"dX L{i + 1} {n_}->{k_}"):
                 ops.dense_backward_dx(b["dz"][i][sl], self._w(i), b["a"][i][sl],
-                                      self.layer_params[i - 1]["activation"], out=b["dz"][i - 1][sl])
+                                      self.layer_params[i - 1]["activation"], out=b["dz"][i - 1][sl], signals=sig)
         if not need_input_grad:
             return None
         k_, n_ = self.layer_params[0]["weights"].shape
         dst = dx_target if dx_target is not None else b["dx"][sl]  # dx_target: the upstream stage's dZ buffer (peer)
+        w_ = wait if (wait is not None and top == 0) else None
+        sig = None
+        if w_ is not None or signal is not None:
+            sig = ops.make_signals(w_[0] if w_ else None, w_[1] if w_ else 0, signal[0] if signal else None,
+                                   signal[1] if signal else 0, signal[2] if signal else None)
         with self._span(f"dX L1 {n_}->{k_}"):
-            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), self._a(0)[sl], self.input_activation, out=dst)
+            ops.dense_backward_dx(b["dz"][0][sl], self._w(0), self._a(0)[sl], self.input_activation, out=dst,
+                                  signals=sig)
         return dst
 
     def step(self, lr: float, rows: Optional[int] = None) -> None:

@@ -32,8 +32,18 @@ def _req(t: torch.Tensor, dtype=None, name="tensor") -> None:
         raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
 
 
+def make_signals(wait_flag: Optional[int] = None, wait_value: int = 0, done_flag: Optional[int] = None,
+                 done_value: int = 0, counter: Optional[int] = None):
+    """A ``ddnn_signals`` for ``dense_forward`` / ``dense_backward_dx`` (raw device addresses of int32 flags): the
+    kernel waits for ``*wait_flag >= wait_value`` before loading its operand and/or its last CTA stores
+    ``done_value`` to ``*done_flag`` (``counter``: 4 zeroed bytes on the device, one per stream)."""
+    if wait_flag is None and done_flag is None:
+        return None
+    return _lib.Signals(wait_flag, int(wait_value), done_flag, int(done_value), counter)
+
+
 def dense_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, act, out: Optional[torch.Tensor] = None,
-                  out_dtype: Optional[torch.dtype] = None) -> torch.Tensor:
+                  out_dtype: Optional[torch.dtype] = None, signals=None) -> torch.Tensor:
     """act(x @ w + bias).  x (B,K), w (K,N) share a dtype (fp32/bf16); bias fp32."""
     _req(x, name="x"); _req(w, x.dtype, "w"); _req(bias, torch.float32, "bias")
     b, k = x.shape
@@ -48,8 +58,12 @@ def dense_forward(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, act, out
     if tuple(out.shape) != (b, n):  # out may be a neighbour GPU's buffer: never hand a mismatched slice to the kernel
         raise ValueError(f"dense_forward: out has shape {tuple(out.shape)}, expected {(b, n)}")
     with torch.cuda.device(x.device):
-        check(lib.ddnn_dense_forward(_p(x), _p(w), _p(bias), _p(out), b, k, n, act_id, _DT[x.dtype], _DT[out.dtype],
-                                     _stream(x)))
+        if signals is None:
+            check(lib.ddnn_dense_forward(_p(x), _p(w), _p(bias), _p(out), b, k, n, act_id, _DT[x.dtype],
+                                         _DT[out.dtype], _stream(x)))
+        else:
+            check(lib.ddnn_dense_forward_signalled(_p(x), _p(w), _p(bias), _p(out), b, k, n, act_id, _DT[x.dtype],
+                                                   _DT[out.dtype], signals, _stream(x)))
     return out
 
 
@@ -89,7 +103,7 @@ def softmax_ce(z: torch.Tensor, labels: torch.Tensor, dz: torch.Tensor, row_loss
 
 
 def dense_backward_dx(dz: torch.Tensor, w: torch.Tensor, a_prev: Optional[torch.Tensor], act_prev,
-                      out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                      out: Optional[torch.Tensor] = None, signals=None) -> torch.Tensor:
     """(dz @ w.T) * f'(a_prev) with f' of the previous layer's activation."""
     _req(dz, name="dz"); _req(w, dz.dtype, "w")
     b, n = dz.shape
@@ -106,9 +120,13 @@ def dense_backward_dx(dz: torch.Tensor, w: torch.Tensor, a_prev: Optional[torch.
         raise ValueError(f"dense_backward_dx: out has shape {tuple(out.shape)}, expected {(b, k)}")
     if a_prev is not None and act_id != ACT_LINEAR and tuple(a_prev.shape) != (b, k):
         raise ValueError(f"dense_backward_dx: a_prev has shape {tuple(a_prev.shape)}, expected {(b, k)}")
+    ap = _p(a_prev if act_id != ACT_LINEAR else None)
     with torch.cuda.device(dz.device):
-        check(lib.ddnn_dense_backward_dx(_p(dz), _p(w), _p(a_prev if act_id != ACT_LINEAR else None), _p(out), b, k,
-                                         n, act_id, _DT[dz.dtype], _stream(dz)))
+        if signals is None:
+            check(lib.ddnn_dense_backward_dx(_p(dz), _p(w), ap, _p(out), b, k, n, act_id, _DT[dz.dtype], _stream(dz)))
+        else:
+            check(lib.ddnn_dense_backward_dx_signalled(_p(dz), _p(w), ap, _p(out), b, k, n, act_id, _DT[dz.dtype],
+                                                       signals, _stream(dz)))
     return out
 
 

@@ -22,6 +22,8 @@ from __future__ import annotations
 
 from typing import List, Optional, Sequence, Tuple
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -112,7 +114,9 @@ class PipelineStage:
             _lib.check(_lib.lib.ddnn_ipc_import(C.cast(buf, C.c_void_p), off, C.byref(out)))
             return tensor_from_ptr(out.value, shape, getattr(torch, dt.split(".")[1]), dev)
 
-        peer = {"key": key, "flags": flags, "M": n_micro}
+        # tile counters of the GEMMs that publish a flag themselves (one per direction: both run on this stream)
+        peer = {"key": key, "flags": flags, "M": n_micro, "counters": torch.zeros((2,), dtype=torch.int32, device=dev),
+                "fused": bool(getattr(L, "supports_signals", False)) and os.environ.get("DDNN_FUSED_FLAGS", "1") != "0"}
         if not self.last:
             nxt = everyone[self.rank + 1]
             peer["next_a0"], peer["next_flags"] = imp(nxt["a0"]), imp(nxt["flags"])
@@ -142,6 +146,12 @@ class PipelineStage:
         P = self._peer
         self._t += 1
         t = self._t
+        fused = P["fused"]
+        my_flags = P["flags"].data_ptr()
+        cnt = P["counters"].data_ptr()
+        # with fused flags the arrival wait rides in the first GEMM of a micro-batch and the departure flag in the
+        # last one (ddnn_signals): consecutive GEMMs stay adjacent in the stream and keep their programmatic
+        # dependent launch; otherwise a stream memory wait before and a one-thread flag kernel after
         with torch.cuda.device(L.device):
             # ---- forward: the last local layer's epilogue stores into the next GPU's input buffer ----
             in_place = self.first and self._adopt_input(x)
@@ -149,27 +159,41 @@ class PipelineStage:
                 n = r1 - r0
                 if ready is not None:
                     torch.cuda.current_stream(L.device).wait_event(ready[m])  # host copy of these rows has landed
+                wait = signal = None
                 if not self.first:
-                    self._flag_wait(m, t)                    # micro-batch m of step t has landed here
+                    if fused:
+                        wait = (my_flags + 4 * m, t)
+                    else:
+                        self._flag_wait(m, t)                # micro-batch m of step t has landed here
                 if not self.last and m == 0 and t > 1:
                     self._flag_wait(2 * M, t - 1)            # rank+1 is done with my step t-1 activations
                 tgt = None if self.last else P["next_a0"][r0:r1]
-                L.forward_train(x[r0:r1] if (self.first and not in_place) else None, r0, n, out_target=tgt)
-                if not self.last:
+                if fused and not self.last:
+                    signal = (P["next_flags"].data_ptr() + 4 * m, t, cnt)
+                kw = {"wait": wait, "signal": signal} if fused else {}
+                L.forward_train(x[r0:r1] if (self.first and not in_place) else None, r0, n, out_target=tgt, **kw)
+                if not self.last and not fused:
                     self._flag_write(P["next_flags"], m, t)
             # ---- backward: the dX epilogue stores dZ into the previous GPU's gradient buffer ----
             loss = None
+            has_dx = (not self.first) or len(L.layer_params) > 1   # is there a dX kernel to carry the wait?
             for m, (r0, r1) in enumerate(slices):
                 n = r1 - r0
+                wait = signal = None
                 if self.last:
                     loss = L.loss_and_grad(labels[r0:r1], r0, denom=rows, accumulate=m > 0)
+                elif fused and has_dx:
+                    wait = (my_flags + 4 * (M + m), t)
                 else:
                     self._flag_wait(M + m, t)
                 if not self.first and m == 0 and t > 1:
                     self._flag_wait(2 * M + 1, t - 1)        # rank-1 is done with my step t-1 gradients
                 tgt = None if self.first else P["prev_dz"][r0:r1]
-                L.backward(r0, n, need_input_grad=not self.first, dx_target=tgt)
-                if not self.first:
+                if fused and not self.first:
+                    signal = (P["prev_flags"].data_ptr() + 4 * (M + m), t, cnt + 4)
+                kw = {"wait": wait, "signal": signal} if fused else {}
+                L.backward(r0, n, need_input_grad=not self.first, dx_target=tgt, **kw)
+                if not self.first and not fused:
                     self._flag_write(P["prev_flags"], M + m, t)
             # ---- update, then hand the receive buffers back to the neighbours ----
             L.step(lr, rows)

@@ -29,7 +29,8 @@ class Trainer:
         self.cfg = cfg
         self.lr = float(cfg.get("learning_rate", 0.01))
         dtype = dtype or cfg.get("dtype", "f32")
-        in_dim = input_dim if input_dim is not None else int(np.asarray(params[0]["weights"]).shape[0])
+        w0 = params[0]["weights"]  # numpy / nested list / torch tensor on any device
+        in_dim = input_dim if input_dim is not None else int(w0.shape[0] if hasattr(w0, "shape") else len(w0))
         self.layer = Layer.from_params(params, in_dim, container_name="trainer", dtype=dtype, device=device,
                                        is_output=True)
         self.device = self.layer.device

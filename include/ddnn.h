@@ -242,6 +242,35 @@ int ddnn_ipc_import(const void* handle64, int64_t offset, void** ptr);
 int ddnn_flag_write(int32_t* flag, int32_t value, void* stream);
 int ddnn_flag_wait(const int32_t* flag, int32_t value, void* stream);
 
+/*
+ * Pipeline signalling folded into a GEMM (no reference counterpart; replaces the per-hop RPC completion of
+ * /root/reference/src/grpc_node.py:130-135).  With a separate ddnn_flag_wait before and ddnn_flag_write after every
+ * micro-batch GEMM the kernels of a stage no longer follow each other directly in the stream, so programmatic
+ * dependent launch cannot overlap them; the *_signalled entry points move both ends into the kernel:
+ *   wait_flag  (nullable): the kernel's operand loader polls  *wait_flag >= wait_value  (acquire, system scope)
+ *              before its first load of X / dZ -- the operand another GPU stores into this GPU's memory;
+ *   done_flag  (nullable): the last CTA to finish stores done_value to *done_flag (local or peer-mapped) after a
+ *              system-scope fence, i.e. after every tile of the output is visible to the flag's reader;
+ *   counter    : 4 bytes of device memory owned by the caller, zero before the first use, shared only by kernels
+ *              of ONE stream (each GEMM leaves it at zero); required when done_flag is given.
+ * On shapes / dtypes that do not run on the tcgen05 kernels the same effect is produced with ddnn_flag_wait, the
+ * plain kernel and ddnn_flag_write.  sig == NULL makes them identical to the plain entry points.  The polling
+ * kernel occupies the GPU until the flag arrives: the producer must not depend on later work of this stream.
+ */
+typedef struct ddnn_signals {
+  const int32_t* wait_flag;
+  int32_t wait_value;
+  int32_t* done_flag;
+  int32_t done_value;
+  uint32_t* counter;
+} ddnn_signals;
+int ddnn_dense_forward_signalled(const void* X, const void* W, const float* bias, void* A,
+                                 int64_t B, int64_t K, int64_t N, int act, int dtype, int out_dtype,
+                                 const ddnn_signals* sig, void* stream);
+int ddnn_dense_backward_dx_signalled(const void* dZ, const void* W, const void* Aprev, void* dZprev,
+                                     int64_t B, int64_t K, int64_t N, int act_prev, int dtype,
+                                     const ddnn_signals* sig, void* stream);
+
 /* Count of kernels this library has launched in this process (bench.py gpu_launches). */
 int64_t ddnn_launch_count(void);
 

@@ -72,7 +72,63 @@ def load_manual_forward():
     return ns["forward_pass"]
 
 
+def load_reference_model_class():
+    """scripts/generate_mnist_pytorch.py downloads MNIST and trains at import; take only its model definition
+    (`class FCNN`, :22-34) -- the reference's own statement of the 784-128-64-10 network whose loss is
+    `nn.CrossEntropyLoss()` on the logits (:37)."""
+    src = open(os.path.join(REF, "scripts", "generate_mnist_pytorch.py")).read()
+    body = src[src.index("class FCNN"):src.index("# Instantiate the model")]
+    import torch
+    import torch.nn as nn
+    import torch.nn.functional as F
+    ns = {"torch": torch, "nn": nn, "F": F}
+    exec(compile(body, "generate_mnist_pytorch_FCNN", "exec"), ns)
+    return ns["FCNN"]
+
+
+def sgd_trajectory():
+    """a6-a8 (softmax-CE, backward, SGD) have no implementation in the reference's src/; the one place the
+    reference states training semantics is its torch script.  This mints an N-step trajectory from THAT model
+    class and loss (float64, optimizer swapped from Adam to plain SGD as north_star mandates) on seeded synthetic
+    data in the reference client's batch order (sequential, ragged tail: run_grpc_inference.py:198-205).  The
+    fixture therefore comes from reference-authored code + torch autograd, not from oracle/."""
+    import torch
+    from ddnn_b200.config import batch_slices, synthetic_batch
+    FCNN = load_reference_model_class()
+    torch.manual_seed(0)
+    model = FCNN()
+    # start from float32-representable weights (what a GPU fp32 run can be given exactly), then go to float64
+    for prm in model.parameters():
+        prm.data = prm.data.float().double()
+    crit = torch.nn.CrossEntropyLoss()
+    lr, bs, epochs, n = 0.05, 128, 2, 1000
+    opt = torch.optim.SGD(model.parameters(), lr=lr)
+    x, y = synthetic_batch(n, 784, 10, seed=21)
+    fcs = [model.fc1, model.fc2, model.fc3]
+    out = {"lr": np.float64(lr), "batch_size": np.int64(bs), "epochs": np.int64(epochs), "rows": np.int64(n),
+           "data_seed": np.int64(21)}
+    for i, fc in enumerate(fcs):  # exporter convention (pytorch.py:68-103): one row of fc.weight per neuron -> W = weight.T
+        out[f"w{i}_init"] = fc.weight.detach().numpy().T.astype(np.float32)
+        out[f"b{i}_init"] = fc.bias.detach().numpy().astype(np.float32)
+    losses = []
+    xt, yt = torch.as_tensor(x, dtype=torch.float64), torch.as_tensor(y, dtype=torch.long)
+    for _ in range(epochs):
+        for (a, b) in batch_slices(n, bs):
+            opt.zero_grad()
+            loss = crit(model(xt[a:b]), yt[a:b])
+            loss.backward()
+            opt.step()
+            losses.append(float(loss.item()))
+    out["losses"] = np.array(losses)
+    for i, fc in enumerate(fcs):
+        out[f"w{i}_final"] = fc.weight.detach().numpy().T.copy()
+        out[f"b{i}_final"] = fc.bias.detach().numpy().copy()
+    np.savez_compressed(os.path.join(HERE, "golden_sgd_trajectory.npz"), **out)
+    print("wrote", os.path.join(HERE, "golden_sgd_trajectory.npz"), f"({len(losses)} steps)")
+
+
 def main():
+    sgd_trajectory()
     grpc_node, fcnn = import_reference()
     from ddnn_b200.config import make_config, make_params, params_to_layers
 

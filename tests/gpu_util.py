@@ -36,3 +36,14 @@ def elementwise_ok(got, ref, rtol: float, atol: float) -> bool:
     ref = np.asarray(ref, dtype=np.float64)
     assert got.shape == ref.shape, (got.shape, ref.shape)
     return bool(np.all(np.abs(got - ref) <= rtol * np.abs(ref) + atol))
+
+
+def cond_ok(got, ref, cond, tol: float) -> bool:
+    """Elementwise bound for a sum of products: |got - ref| <= tol * cond for EVERY element, where ``cond`` is the
+    same expression evaluated on absolute values (sum_k |a_k| |b_k|, the condition sum of that element).  Unlike a
+    plain relative check it stays meaningful for elements that cancel to ~0, and unlike the normalised-max check it
+    does not let a small element hide behind the tensor's largest one."""
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape == np.asarray(cond).shape
+    return bool(np.all(np.abs(got - ref) <= tol * np.asarray(cond) + 1e-300))

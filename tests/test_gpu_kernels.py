@@ -4,7 +4,7 @@ import pytest
 import torch
 
 import oracle
-from gpu_util import BF16_ACT_TOL, BF16_GRAD_TOL, F32_TOL, rel_err, to_dev, to_np
+from gpu_util import BF16_ACT_TOL, BF16_GRAD_TOL, F32_TOL, cond_ok, rel_err, to_dev, to_np
 
 pytestmark = pytest.mark.gpu
 
@@ -30,6 +30,8 @@ def test_forward_f32(cuda_device, shape, act):
     ref = oracle.activate(np.dot(x, w) + bias, act)
     got = ops.dense_forward(to_dev(x), to_dev(w), to_dev(bias), act)
     assert rel_err(to_np(got), ref) < F32_TOL
+    if act != "softmax":  # every element within 1e-5 of its own condition sum (relu / sigmoid / identity are 1-Lipschitz)
+        assert cond_ok(to_np(got), ref, np.dot(np.abs(x), np.abs(w)) + np.abs(bias), F32_TOL)
 
 
 @pytest.mark.parametrize("shape", SHAPES)
@@ -65,6 +67,8 @@ def test_backward_dw_f32(cuda_device, shape):
     dw, db = ops.dense_backward_dw(to_dev(x), to_dev(dz))
     assert rel_err(to_np(dw), np.dot(x.T, dz)) < F32_TOL
     assert rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+    assert cond_ok(to_np(dw), np.dot(x.T, dz), np.dot(np.abs(x).T, np.abs(dz)), F32_TOL)
+    assert cond_ok(to_np(db), dz.sum(axis=0), np.abs(dz).sum(axis=0), F32_TOL)
 
 
 @pytest.mark.parametrize("shape", [(64, 784, 128), (50, 64, 10), (257, 100, 130)])

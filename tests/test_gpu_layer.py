@@ -141,6 +141,25 @@ def test_n_step_weight_trajectory_f32(cuda_device):
         assert rel_err(g["biases"], r["biases"]) < F32_TOL
 
 
+def test_trajectory_of_the_reference_model_class_f32(cuda_device):
+    """The 16-step SGD trajectory minted from the reference's own FCNN class + nn.CrossEntropyLoss
+    (scripts/generate_mnist_pytorch.py:22-37; tests/golden/make_golden.py, torch autograd in float64): a fixture
+    for softmax-CE / backward / SGD that does not come from oracle/.  Same initial weights, same seeded data, the
+    reference client's batch order; losses and final weights within the fp32 bound."""
+    from conftest import GOLDEN
+    from ddnn_b200 import Trainer
+    g = dict(np.load(os.path.join(GOLDEN, "golden_sgd_trajectory.npz")))
+    params = [{"weights": g[f"w{i}_init"], "biases": g[f"b{i}_init"], "activation": a}
+              for i, a in enumerate(["relu", "relu", "softmax"])]
+    x, y = synthetic_batch(int(g["rows"]), 784, 10, seed=int(g["data_seed"]))
+    t = Trainer(params)
+    got = t.fit((x, y), epochs=int(g["epochs"]), batch_size=int(g["batch_size"]), lr=float(g["lr"]))
+    np.testing.assert_allclose(got, g["losses"], rtol=F32_TOL)
+    for i, p in enumerate(t.export_params()):
+        assert rel_err(p["weights"], g[f"w{i}_final"]) < F32_TOL
+        assert rel_err(p["biases"], g[f"b{i}_final"]) < F32_TOL
+
+
 def test_cuda_graph_step_equals_eager(cuda_device):
     from ddnn_b200 import Trainer
     dims, acts = [784, 32, 16, 10], ["relu", "relu", "softmax"]

@@ -176,3 +176,46 @@ def test_cta_pair_kernels(cuda_device, bkn):
         assert torch.equal(ops.dense_backward_dw(x2, dz2)[0], dw)
     finally:
         _lib.set_cta_pairs(True)
+
+
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("bkn", [(512, 256, 256), (4096, 512, 4096)])
+def test_signals_folded_into_the_gemm(cuda_device, bkn):
+    """ddnn_dense_forward_signalled / ddnn_dense_backward_dx_signalled (single-CTA and CTA-pair kernels): same bits as
+    the plain entry points; the last CTA publishes done_flag and leaves the tile counter at zero; a kernel whose
+    wait_flag is not yet set starts, polls, and finishes once another stream sets the flag."""
+    from ddnn_b200 import _lib, ops
+    b, k, n = bkn
+    rng = np.random.default_rng(30)
+    x = to_dev(rng.random((b, k)) - 0.25, torch.bfloat16)
+    w = to_dev(rng.standard_normal((k, n)) / np.sqrt(k), torch.bfloat16)
+    bias = to_dev(rng.standard_normal(n) * 0.1)
+    flags = torch.zeros((4,), dtype=torch.int32, device="cuda")
+    counter = torch.zeros((1,), dtype=torch.int32, device="cuda")
+    plain = ops.dense_forward(x, w, bias, "relu")
+    flags[0] = 7
+    sig = ops.make_signals(flags.data_ptr(), 7, flags.data_ptr() + 4, 42, counter.data_ptr())
+    for _ in range(2):  # twice: the counter must have been left at zero
+        got = ops.dense_forward(x, w, bias, "relu", signals=sig)
+        torch.cuda.synchronize()
+        assert torch.equal(got, plain) and int(flags[1]) == 42 and int(counter[0]) == 0
+        flags[1] = 0
+    # dX: wait only (no publish)
+    dz = to_dev(rng.standard_normal((b, n)) / b, torch.bfloat16)
+    a_prev = to_dev(oracle.activate(rng.standard_normal((b, k)), "relu"), torch.bfloat16)
+    plain_dx = ops.dense_backward_dx(dz, w, a_prev, "relu")
+    got_dx = ops.dense_backward_dx(dz, w, a_prev, "relu", signals=ops.make_signals(flags.data_ptr(), 7))
+    assert torch.equal(got_dx, plain_dx)
+    # a wait that is satisfied only later, from another stream
+    if b * n <= 512 * 256:  # few CTAs: the flag kernel of the other stream always finds a free SM
+        torch.cuda.synchronize()
+        side = torch.cuda.Stream()
+        sig = ops.make_signals(flags.data_ptr() + 8, 5, flags.data_ptr() + 12, 9, counter.data_ptr())
+        with torch.cuda.stream(side):
+            late = ops.dense_forward(x, w, bias, "relu", signals=sig)
+        import time
+        time.sleep(0.05)
+        assert int(flags[3].item()) == 0  # still polling: nothing published
+        _lib.check(_lib.lib.ddnn_flag_write(flags.data_ptr() + 8, 5, torch.cuda.current_stream().cuda_stream))
+        side.synchronize()
+        assert torch.equal(late, plain) and int(flags[3]) == 9

@@ -1,6 +1,7 @@
 """The oracle against the reference's golden vectors (tests/golden, minted by running the
 unmodified reference) and against torch autograd for the parts the reference lacks."""
 import json
+import os
 
 import numpy as np
 import pytest
@@ -8,6 +9,7 @@ import torch
 
 import oracle
 from ddnn_b200.config import make_params, node_config_to_params
+from conftest import GOLDEN
 
 
 def test_kat_bit_exact(golden_small):
@@ -203,3 +205,23 @@ def test_hidden_softmax_and_bad_output_activation():
     a, zs = oracle.forward_all(bad, x)
     with pytest.raises(ValueError):
         oracle.backward(bad, a, zs, y)
+
+
+def test_training_restatement_tracks_the_reference_models_own_trajectory():
+    """tests/golden/golden_sgd_trajectory.npz was minted (make_golden.py) from the reference's OWN model class and
+    loss (scripts/generate_mnist_pytorch.py:22-37: FCNN, nn.CrossEntropyLoss) under torch autograd + plain SGD in
+    float64.  The oracle's softmax-CE / backward / SGD restatement must reproduce its 16 losses and final weights."""
+    from ddnn_b200.config import batch_slices, synthetic_batch
+    g = dict(np.load(os.path.join(GOLDEN, "golden_sgd_trajectory.npz")))
+    params = [{"weights": g[f"w{i}_init"].astype(np.float64), "biases": g[f"b{i}_init"].astype(np.float64),
+               "activation": a} for i, a in enumerate(["relu", "relu", "softmax"])]
+    n, bs = int(g["rows"]), int(g["batch_size"])
+    x, y = synthetic_batch(n, 784, 10, seed=int(g["data_seed"]))
+    losses = []
+    for _ in range(int(g["epochs"])):
+        for (a, b) in batch_slices(n, bs):
+            losses.append(oracle.train_step(params, x[a:b], y[a:b], float(g["lr"])))
+    np.testing.assert_allclose(losses, g["losses"], rtol=1e-12)
+    for i, p in enumerate(params):
+        np.testing.assert_allclose(p["weights"], g[f"w{i}_final"], rtol=1e-10, atol=1e-14)
+        np.testing.assert_allclose(p["biases"], g[f"b{i}_final"], rtol=1e-10, atol=1e-14)
