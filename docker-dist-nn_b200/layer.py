@@ -288,7 +288,7 @@ class Layer:
 
     def forward_train(self, x: Optional[torch.Tensor], row0: int = 0, rows: Optional[int] = None,
                       out_target: Optional[torch.Tensor] = None, skip_last: int = 0,
-                      wait=None, signal=None) -> torch.Tensor:
+                      wait=None, signal=None, infer: bool = False) -> torch.Tensor:
         """Forward of rows [row0, row0+rows) keeping what backward needs.  ``x`` None means the
         rows are already in ``input_buffer``.  An output node stops at the fp32 logits Z
         (softmax is fused into ``loss_and_grad``).  ``out_target`` (rows, N_last) redirects the
@@ -297,7 +297,9 @@ class Layer:
         (this node never reads its own last output).  ``wait = (flag_address, value)`` makes the FIRST local
         layer's kernel wait for that flag before it loads its input rows, ``signal = (flag_address, value,
         counter_address)`` makes the LAST local layer's kernel publish that flag when its output is complete
-        (``ddnn_signals``): the pipeline's arrival / departure flags without a launch of their own."""
+        (``ddnn_signals``): the pipeline's arrival / departure flags without a launch of their own.
+        ``infer=True`` is the forward-only relay of the reference chain (grpc_node.py:75-97) on the same buffers:
+        an output node applies its real activation (softmax) and any activation is allowed."""
         a = self._bufs["a"]
         if x is not None:
             rows = x.shape[0]
@@ -319,7 +321,9 @@ class Layer:
             if i >= n_layers - int(skip_last):  # the fused output-layer (1) / two-layer tail (2) step runs these
                 break
             act = p["activation"]
-            if last and self.is_output:
+            if infer:
+                pass
+            elif last and self.is_output:
                 if act in ("relu", "sigmoid"):
                     raise ValueError(f"output activation {act!r} has no softmax-CE loss")
                 act = "linear"  # logits; softmax happens inside the fused CE kernel

@@ -322,19 +322,54 @@ class PipelineStage:
         return losses_host.tolist() if self.last else []
 
     def infer(self, x: Optional[torch.Tensor], rows: int, micro_batches: int) -> Optional[torch.Tensor]:
-        """Forward-only relay (what the reference chain does): the last stage returns the
-        softmax output for all rows."""
+        """Forward-only relay of ``rows`` examples in ``micro_batches`` chunks -- what the reference chain does
+        with one request (grpc_node.py:103-147), pipelined: the last stage returns the output node's activations
+        (fp32, (rows, N_out)) for all rows, the other stages None.  Uses the stage's resident buffers (no
+        allocation per micro-batch) and the configured transport: with ``peer`` the last local GEMM of a stage
+        stores straight into the next GPU's input buffer and the arrival flags ride in the GEMMs."""
         L = self.layer
-        outs = []
-        for (r0, r1) in micro_batch_slices(rows, micro_batches):
-            if self.first:
-                cur = x[r0:r1]
-            else:
-                cur = torch.empty((r1 - r0, L.expected_input_dim), dtype=L.wire_dtype, device=L.device)
-                self._recv(cur, self.rank - 1)
-            out = L.process_matrix(cur)
+        L.begin_batch(rows)
+        slices = micro_batch_slices(rows, micro_batches)
+        M = len(slices)
+        if self.transport != "peer":
+            for (r0, r1) in slices:
+                n = r1 - r0
+                if self.first:
+                    out = L.forward_train(x[r0:r1], r0, infer=True)
+                else:
+                    self._recv(L.input_buffer(r0, n), self.rank - 1)
+                    out = L.forward_train(None, r0, n, infer=True)
+                if not self.last:
+                    self._send(out, self.rank + 1)
+            return L.output_buffer(0, rows) if self.last else None
+        self._peer_setup(rows, M)
+        P = self._peer
+        self._t += 1
+        t = self._t
+        fused = P["fused"]
+        with torch.cuda.device(L.device):
+            in_place = self.first and self._adopt_input(x)
+            for m, (r0, r1) in enumerate(slices):
+                n = r1 - r0
+                wait = signal = None
+                if not self.first:
+                    if fused:
+                        wait = (P["flags"].data_ptr() + 4 * m, t)
+                    else:
+                        self._flag_wait(m, t)
+                if not self.last and m == 0 and t > 1:
+                    self._flag_wait(2 * M, t - 1)            # rank+1 is done with what I sent it last time
+                tgt = None if self.last else P["next_a0"][r0:r1]
+                if fused and not self.last:
+                    signal = (P["next_flags"].data_ptr() + 4 * m, t, P["counters"].data_ptr())
+                kw = {"wait": wait, "signal": signal} if fused else {}
+                L.forward_train(x[r0:r1] if (self.first and not in_place) else None, r0, n, out_target=tgt,
+                                infer=True, **kw)
+                if not self.last and not fused:
+                    self._flag_write(P["next_flags"], m, t)
+            # hand the receive buffers back (a training step after this one waits for both flags of step t)
+            if not self.first:
+                self._flag_write(P["prev_flags"], 2 * M, t)
             if not self.last:
-                self._send(out.to(L.wire_dtype).contiguous(), self.rank + 1)
-            else:
-                outs.append(out)
-        return torch.cat(outs) if outs else None
+                self._flag_write(P["next_flags"], 2 * M + 1, t)
+        return L.output_buffer(0, rows) if self.last else None

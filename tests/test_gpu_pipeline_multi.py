@@ -20,3 +20,33 @@ def test_pipeline_transports_match_single_gpu():
            "127.0.0.1", "--master-port", "29731", os.path.join(REPO, "tools", "check_pipeline.py")]
     r = subprocess.run(cmd, cwd=REPO, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert r.returncode == 0 and "PIPELINE CHECK PASS" in r.stdout, r.stdout[-3000:]
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_eval_driver_over_the_pipeline(tmp_path):
+    """`python -m ddnn_b200.infer --gpus 2`: the reference client's CLI and log lines (run_grpc_inference.py:162-252)
+    with the chain replaced by the forward-only GPU pipeline; the accuracy line must equal the oracle's argmax count
+    on the same exported model, ragged last batch included."""
+    import json
+    import re
+
+    import numpy as np
+
+    import oracle
+    from ddnn_b200.config import make_config, make_params, synthetic_batch
+    dims, acts = [784, 128, 64, 10], ["relu", "relu", "softmax"]
+    cfg = make_config(dims, acts, seed=1, layer_distribution=[2, 1])
+    x, y = synthetic_batch(300, 784, 10, seed=9)
+    ref = oracle.process_matrix(make_params(dims, acts, seed=1), x, 784)
+    want = int((ref.argmax(axis=1) == y).sum())
+    (tmp_path / "model.json").write_text(json.dumps(cfg))
+    (tmp_path / "inputs.json").write_text(json.dumps(
+        {"examples": [{"input": r.tolist(), "label": int(l)} for r, l in zip(x, y)]}))
+    cmd = [sys.executable, "-m", "ddnn_b200.infer", "--gpus", "2", "--config", str(tmp_path / "model.json"),
+           "--inputs", str(tmp_path / "inputs.json"), "--batch-size", "128", "--micro-batches", "3"]
+    r = subprocess.run(cmd, cwd=REPO, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600,
+                       env=dict(os.environ, PYTHONPATH=REPO, DDNN_MASTER_PORT="29743"))
+    assert r.returncode == 0, r.stdout[-3000:]
+    m = re.search(r"Correct predictions: (\d+) out of (\d+)", r.stdout)
+    assert m and int(m.group(2)) == 300 and int(m.group(1)) == want, r.stdout[-3000:]
+    assert "Batch 3/3 completed" in r.stdout

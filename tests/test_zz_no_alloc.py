@@ -102,3 +102,41 @@ def test_layers_beyond_the_scratch_limit_are_refused(cuda_device):
     assert "built-in scratch holds" in e.value.text and "caller-owned workspace" in e.value.text
     torch.cuda.synchronize()
     assert float(dw.min()) == 7.0 and float(db.max()) == 7.0
+
+
+def test_no_device_memory_is_taken_by_the_call(cuda_device):
+    """What the entry point is for: after its first call on a device (which looks up the built-in array's
+    address), further calls leave the device's free memory and torch's allocator untouched -- the driver hands
+    out nothing and nothing is returned, however many layers go through."""
+    rng = np.random.default_rng(23)
+    xd, dzd = to_dev(rng.random((2048, 256))), to_dev(rng.standard_normal((2048, 64)) / 2048)
+    dw = torch.empty((256, 64), device="cuda")
+    db = torch.empty((64,), device="cuda")
+    _static_call(xd, dzd, dw=dw, db=db)      # one-time set-up on this device happens here at the latest
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    for _ in range(5):
+        _static_call(xd, dzd, dw=dw, db=db)
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0
+    assert torch.cuda.memory_allocated() == alloc0 and torch.cuda.memory_reserved() == reserved0
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs a second GPU")
+def test_every_device_gets_its_own_scratch_address(cuda_device):
+    """The array lives once per GPU and its address differs from device to device: a call with cuda:1 current must
+    use cuda:1's copy (the look-up is per device ordinal), and give the regular entry point's result there."""
+    from ddnn_b200 import ops
+    rng = np.random.default_rng(24)
+    x, dz = rng.random((1024, 128)), rng.standard_normal((1024, 32)) / 1024
+    for dev in ("cuda:1", "cuda:0"):
+        with torch.cuda.device(dev):
+            xd, dzd = to_dev(x, device=dev), to_dev(dz, device=dev)
+            dw = torch.empty((128, 32), device=dev)
+            db = torch.empty((32,), device=dev)
+            _static_call(xd, dzd, dw=dw, db=db)
+            ref_dw, ref_db = ops.dense_backward_dw(xd, dzd)
+            assert rel_err(to_np(dw), to_np(ref_dw)) < F32_TOL and rel_err(to_np(db), to_np(ref_db)) < F32_TOL
+            assert rel_err(to_np(dw), x.T @ dz) < F32_TOL
