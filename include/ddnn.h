@@ -9,8 +9,11 @@
  *
  * Conventions
  *  - every pointer is a DEVICE pointer owned by the caller (incl. workspace); the
- *    library allocates no device memory and keeps no state besides a mutex-guarded
- *    cache of TMA descriptors keyed by (pointer, shape);
+ *    library allocates no device memory.  Its state: a mutex-guarded cache of TMA
+ *    descriptors keyed by (pointer, shape), the per-device kernel attributes it has set,
+ *    and the process-wide ddnn_set_* switches below -- test / profiling knobs that select
+ *    between equivalent kernels; set them before serving, not while calls are in flight
+ *    on other threads (the defaults never need changing);
  *  - matrices are row-major, (batch, features); weights are (K = in, N = out) like
  *    grpc_node.py:51 (`np.array([...]).T`);
  *  - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, nothing
@@ -56,7 +59,7 @@ const char* ddnn_last_error(void);
 /* Maps an activation string the way Layer.activate does (grpc_node.py:62-73). */
 int ddnn_activation_from_name(const char* name);
 
-/* Force an engine for subsequent calls of this process (tests / profiling). */
+/* Force an engine for subsequent calls of this process (tests / profiling only: process-wide, see above). */
 int ddnn_set_engine(int engine);
 
 /*
