@@ -95,34 +95,54 @@ def sgd_trajectory():
     import torch
     from ddnn_b200.config import batch_slices, synthetic_batch
     FCNN = load_reference_model_class()
-    torch.manual_seed(0)
-    model = FCNN()
-    # start from float32-representable weights (what a GPU fp32 run can be given exactly), then go to float64
-    for prm in model.parameters():
-        prm.data = prm.data.float().double()
     crit = torch.nn.CrossEntropyLoss()
     lr, bs, epochs, n = 0.05, 128, 2, 1000
-    opt = torch.optim.SGD(model.parameters(), lr=lr)
-    x, y = synthetic_batch(n, 784, 10, seed=21)
-    fcs = [model.fc1, model.fc2, model.fc3]
-    out = {"lr": np.float64(lr), "batch_size": np.int64(bs), "epochs": np.int64(epochs), "rows": np.int64(n),
-           "data_seed": np.int64(21)}
-    for i, fc in enumerate(fcs):  # exporter convention (pytorch.py:68-103): one row of fc.weight per neuron -> W = weight.T
-        out[f"w{i}_init"] = fc.weight.detach().numpy().T.astype(np.float32)
-        out[f"b{i}_init"] = fc.bias.detach().numpy().astype(np.float32)
-    losses = []
-    xt, yt = torch.as_tensor(x, dtype=torch.float64), torch.as_tensor(y, dtype=torch.long)
-    for _ in range(epochs):
-        for (a, b) in batch_slices(n, bs):
-            opt.zero_grad()
-            loss = crit(model(xt[a:b]), yt[a:b])
-            loss.backward()
-            opt.step()
-            losses.append(float(loss.item()))
-    out["losses"] = np.array(losses)
-    for i, fc in enumerate(fcs):
-        out[f"w{i}_final"] = fc.weight.detach().numpy().T.copy()
-        out[f"b{i}_final"] = fc.bias.detach().numpy().copy()
+
+    def run(data_seed):
+        torch.manual_seed(0)
+        model = FCNN()
+        # start from float32-representable weights (what a GPU fp32 run can be given exactly), then go to float64
+        for prm in model.parameters():
+            prm.data = prm.data.float().double()
+        opt = torch.optim.SGD(model.parameters(), lr=lr)
+        x, y = synthetic_batch(n, 784, 10, seed=data_seed)
+        fcs = [model.fc1, model.fc2, model.fc3]
+        out = {"lr": np.float64(lr), "batch_size": np.int64(bs), "epochs": np.int64(epochs), "rows": np.int64(n),
+               "data_seed": np.int64(data_seed)}
+        for i, fc in enumerate(fcs):  # exporter convention (pytorch.py:68-103): one row of fc.weight per neuron -> W = weight.T
+            out[f"w{i}_init"] = fc.weight.detach().numpy().T.astype(np.float32)
+            out[f"b{i}_init"] = fc.bias.detach().numpy().astype(np.float32)
+        losses, min_z = [], np.inf
+        xt, yt = torch.as_tensor(x, dtype=torch.float64), torch.as_tensor(y, dtype=torch.long)
+        for _ in range(epochs):
+            for (a, b) in batch_slices(n, bs):
+                with torch.no_grad():  # smallest |pre-activation| of a ReLU gate in this step
+                    z1 = model.fc1(xt[a:b])
+                    z2 = model.fc2(torch.relu(z1))
+                    min_z = min(min_z, float(z1.abs().min()), float(z2.abs().min()))
+                opt.zero_grad()
+                loss = crit(model(xt[a:b]), yt[a:b])
+                loss.backward()
+                opt.step()
+                losses.append(float(loss.item()))
+        out["losses"] = np.array(losses)
+        out["min_abs_preactivation"] = np.float64(min_z)
+        for i, fc in enumerate(fcs):
+            out[f"w{i}_final"] = fc.weight.detach().numpy().T.copy()
+            out[f"b{i}_final"] = fc.bias.detach().numpy().copy()
+        return out
+
+    # A ReLU gate whose pre-activation is closer to zero than the fp32 forward error (~1e-6 here) flips in ANY fp32
+    # implementation and moves a weight by lr * x * dz / B ~ 1e-5: with 384 000 gates along the trajectory a few
+    # are always that marginal (seed 21: one at 5e-8).  The data seed is the first one whose trajectory has none
+    # below 2e-6, so that the fixture tests the arithmetic and not the luck of a gate.
+    for data_seed in range(21, 400):
+        out = run(data_seed)
+        if float(out["min_abs_preactivation"]) >= 2e-6:
+            break
+    else:
+        raise RuntimeError("no data seed without a marginal ReLU gate")
+    losses = out["losses"]
     np.savez_compressed(os.path.join(HERE, "golden_sgd_trajectory.npz"), **out)
     print("wrote", os.path.join(HERE, "golden_sgd_trajectory.npz"), f"({len(losses)} steps)")
 

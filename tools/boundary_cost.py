@@ -45,14 +45,20 @@ def main():
         return e0.elapsed_time(e1) / (reps * m)
 
     fl = 2.0 * mb * width * width
-    for name, pdl, boundary in (("stream-ordered chain, PDL on", 1, False), ("PDL off", 0, False),
-                                ("flag wait + flag kernel between GEMMs, PDL on", 1, True),
-                                ("flag wait + flag kernel between GEMMs, PDL off", 0, True),
-                                ("stream-ordered chain, PDL on (again)", 1, False)):
-        _lib.lib.ddnn_set_pdl(pdl)
-        t = timed(boundary)
-        print(f"{width}x{width}, {mb}-row micro-batches: {name}: {t * 1e3:.1f} us per GEMM, {fl / t / 1e9:.0f} TFLOP/s",
-              flush=True)
+    variants = (("stream-ordered chain, PDL on", 1, False), ("PDL off", 0, False),
+                ("flag wait + flag kernel between GEMMs, PDL on", 1, True),
+                ("flag wait + flag kernel between GEMMs, PDL off", 0, True))
+    for _ in range(int(os.environ.get("WARM", "40"))):  # reach the clocks the power cap leaves before measuring
+        chain(False)
+    acc = {v[0]: [] for v in variants}
+    for _ in range(int(os.environ.get("ROUNDS", "4"))):  # interleaved: drift hits every variant alike
+        for name, pdl, boundary in variants:
+            _lib.lib.ddnn_set_pdl(pdl)
+            acc[name].append(timed(boundary))
+    for name, ts in acc.items():
+        t = sum(ts) / len(ts)
+        print(f"{width}x{width}, {mb}-row micro-batches: {name}: {t * 1e3:.1f} us per GEMM, {fl / t / 1e9:.0f} TFLOP/s  "
+              f"(rounds: {', '.join(f'{v * 1e3:.1f}' for v in ts)})", flush=True)
     _lib.lib.ddnn_set_pdl(1)
 
 
