@@ -161,6 +161,10 @@ def cpu_threads() -> int:
 
 DEFAULT_WORKLOAD = "wide8x16384"
 LR = 0.01
+# wide nets: order of a pipeline step and rows per weight-gradient chunk (the same at every GPU count: the chunk
+# boundaries are part of the arithmetic, so losses and weights stay bit-identical from 1 to 8 GPUs)
+PIPE_SCHEDULE = "zb"
+PIPE_DW_CHUNK_ROWS = 16384
 # rows of one CPU step (a bounded sample of the workload's batch): the oracle's float64 GEMMs are compute-bound
 # from ~100 rows on, and 20 + 5 steps must end within minutes on the host cores
 CPU_ROWS = {"mnist4096": 4096, "narrow65536": 8192, "wide4x8192": 256, "wide8x16384": 256}
@@ -580,8 +584,10 @@ def wide_entry(workload, steps, warmup, device, rank, world, barrier, max_over_r
                               input_activation=(acts[lo - 1] if lo > 0 else "linear"), is_output=(hi == n_layers))
     del params
     transport = os.environ.get("DDNN_TRANSPORT", "peer") if world > 1 else "local"
-    schedule = os.environ.get("DDNN_SCHEDULE", "gpipe")
-    stage = PipelineStage(layer, rank, world, transport=transport if world > 1 else "nccl", schedule=schedule)
+    schedule = os.environ.get("DDNN_SCHEDULE", PIPE_SCHEDULE)
+    dw_chunk = int(os.environ.get("DDNN_DW_CHUNK", str(max(1, PIPE_DW_CHUNK_ROWS // (rows // micro))))) or None
+    stage = PipelineStage(layer, rank, world, transport=transport if world > 1 else "nccl", schedule=schedule,
+                          dw_chunk=dw_chunk, layers_per_stage=[b - a for a, b in stage_assignment(n_layers, world)])
     first, last = rank == 0, rank == world - 1
     # batch and labels from their own generators: the same data whatever the stage count
     x = torch.rand((rows, dims[0]), device=device, generator=torch.Generator(device=device).manual_seed(0)
@@ -607,12 +613,14 @@ def wide_entry(workload, steps, warmup, device, rank, world, barrier, max_over_r
     value = rows * steps / (ms / 1e3)
     fps = flops_per_sample(dims)
     ent = {"workload": workload, "stages": world, "layers_per_stage": hi - lo, "micro_batches": micro,
-           "transport": transport, "schedule": schedule, "rows_per_step": rows, "steps": steps, "value": value,
+           "transport": transport, "schedule": schedule, "dw_chunk_micro_batches": dw_chunk, "rows_per_step": rows, "steps": steps, "value": value,
            "unit": "samples/s", "ms_per_step": ms / steps, "scaling": "strong", "dtype": dtype,
            "launches_per_step": int(launches), "tflops_total": value * fps / 1e12,
            "tensor_frac_of_measured_burst": value * fps / 1e12 / (world * peaks["bf16_tflops"]),
            "tensor_frac_of_measured_sustained": value * fps / 1e12 / (world * peaks["bf16_tflops_sustained"]),
-           "bubble_bound": (3 * micro) / (3 * micro + 2 * (world - 1)),
+           # slots of one GEMM per micro-batch and layer: 3M of work per stage (2M + M(L-1)/L on the first, whose
+           # layer 1 has no dX) plus the fill / drain slots the order leaves idle: 2(S-1) GPipe, (S-1) zero-bubble
+           "bubble_bound": (3 * micro) / (3 * micro + (2 if schedule == "gpipe" else 1) * (world - 1)),
            "loss_first_steps": first_losses, "loss_first_steps_hex": [float(v).hex() for v in first_losses],
            "weights_checksum": f"{sum(sums) & 0xFFFFFFFFFFFFFFFF:016x}",
            "weights_checksum_per_layer": [f"{v & 0xFFFFFFFFFFFFFFFF:016x}" for v in sums],
@@ -632,6 +640,9 @@ def wide_entry(workload, steps, warmup, device, rank, world, barrier, max_over_r
             work[f"forward L{i + 1} {k}->{n}"] = (2.0 * mb * k * n, mb * k * 2 + k * n * 2 + mb * n * (4 if is_out else 2))
             work[f"dX L{i + 1} {n}->{k}"] = (2.0 * mb * k * n, mb * n * 2 + k * n * 2 + 2 * mb * k * 2)
             work[f"dW+SGD L{i + 1} {k}x{n}"] = (2.0 * rows * k * n, rows * k * 2 + rows * n * 2 + 2 * k * n * 4 + k * n * 2)
+            crows = (dw_chunk or micro) * mb
+            work[f"dW chunk L{i + 1} {k}x{n}"] = (2.0 * crows * k * n, crows * (k + n) * 2 + 2 * k * n * 4)
+            work[f"SGD apply L{i + 1} {k}x{n}"] = (2.0 * k * n, k * n * (4 + 4 + 4 + 2))
         work[f"softmax-CE N={dims[-1]}"] = (5.0 * mb * dims[-1], mb * dims[-1] * 6 + mb * 8)
         acc = {}
         for name, e0, e1 in spans:
@@ -746,7 +757,7 @@ def main():
         "tensor_frac_of_measured_sustained": head["value"] * fps / 1e12 / (world * peaks["bf16_tflops_sustained"]),
         "peaks": peaks,
     }
-    for k in ("e2e", "roofline", "kernels", "stages", "transport", "schedule", "bubble_bound", "loss_first_steps",
+    for k in ("e2e", "roofline", "kernels", "stages", "transport", "schedule", "dw_chunk_micro_batches", "bubble_bound", "loss_first_steps",
               "loss_first_steps_hex", "weights_checksum", "weights_checksum_per_layer", "checksum_of", "cuda_graph", "l2",
               "step_hbm_bytes_per_sample", "step_hbm_frac_of_measured"):
         if k in head:

@@ -51,6 +51,8 @@ SYMBOLS = {
     "ddnn_dense_backward_dw_sgd": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
                                              _i32, _vp, _sz, _vp]),
     "ddnn_dw_workspace_bytes": (_sz, [_i64, _i64, _i64, _i32]),
+    "ddnn_dense_backward_dw_accumulate": (C.c_int, [_vp, _vp, _vp, _vp, _i32, _i64, _i64, _i64, _i32, _vp, _sz, _vp]),
+    "ddnn_sgd_apply": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _f32, _i64, _i64, _vp]),
     "ddnn_dense_backward_dw_sgd_static": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32, _i64, _i64, _i64,
                                                     _i32, _vp]),
     "ddnn_output_layer_train": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f32, _i32,

@@ -393,6 +393,38 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
   return reduce_dw(dw_part, db_part, splits, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
 }
 
+int ddnn_dense_backward_dw_accumulate(const void* X, const void* dZ, float* dW_acc, float* db_acc, int first, int64_t B,
+                                      int64_t K, int64_t N, int dtype, void* workspace, size_t workspace_bytes,
+                                      void* stream) {
+  if (!dW_acc || !db_acc) {
+    set_error("ddnn_dense_backward_dw_accumulate: null accumulator");
+    return DDNN_ERR_ARG;
+  }
+  if (first)  // plain gradient store
+    return ddnn_dense_backward_dw_sgd(X, dZ, nullptr, nullptr, nullptr, dW_acc, db_acc, 0.0f, 0, B, K, N, dtype,
+                                      workspace, workspace_bytes, stream);
+  // acc - (-1) * g: the update epilogue with the accumulator as the "weight" (an FMA with multiplier 1: exact sum,
+  // rounded once)
+  return ddnn_dense_backward_dw_sgd(X, dZ, dW_acc, nullptr, db_acc, nullptr, nullptr, -1.0f, 1, B, K, N, dtype,
+                                    workspace, workspace_bytes, stream);
+}
+
+int ddnn_sgd_apply(float* W_master, void* W_shadow, float* bias, const float* dW, const float* db, float lr, int64_t K,
+                   int64_t N, void* stream) {
+  int rc = check_dims("ddnn_sgd_apply", 1, K, N);
+  if (rc) return rc;
+  if (!W_master || !bias || !dW || !db) {
+    set_error("ddnn_sgd_apply: null pointer");
+    return DDNN_ERR_ARG;
+  }
+  if (N % 4 != 0) {  // the reducer reads gradient rows at a pitch of N rounded up to 4
+    set_error("ddnn_sgd_apply: N = %lld is not a multiple of 4", (long long)N);
+    return DDNN_ERR_UNSUPPORTED;
+  }
+  // a one-split "reduction": W -= lr * dW, bias -= lr * db, shadow refreshed, in one launch
+  return reduce_dw(dW, db, 1, K, N, W_master, W_shadow, bias, nullptr, nullptr, lr, 1, (cudaStream_t)stream);
+}
+
 size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {
   if (B <= 0 || K <= 0 || N <= 0) return 0;
   if (!outlayer_fused_ok(nullptr, K, N, dtype)) return 0;  // shapes the entry point rejects need no scratch

@@ -12,6 +12,7 @@
 // fp32 master + bf16 shadow write (dW), or fp32 store (gradient output / split-K partial).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -721,6 +722,13 @@ int launch_one(const CUtensorMap& ta, const CUtensorMap& tb, const UmmaParams& p
 
 std::atomic<int> g_use_pair{1};  // 1: CTA-pair (cta_group::2) kernel for large BN = 256 problems
 
+// Measurement knobs (environment, read once): DDNN_DBG_GROUP_M overrides the rasterisation group of the pair
+// kernel (in 256-row blocks), DDNN_DBG_PAIRS its number of CTA pairs.  Unset in normal use.
+static int dbg_env(const char* name) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : 0;
+}
+
 template <bool A_MN, bool B_MN, int EPI, int EW>
 int launch_pair_ew(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, cudaStream_t st) {
   auto kern = umma_pair_gemm_kernel<A_MN, B_MN, EPI, EW>;
@@ -735,9 +743,12 @@ int launch_pair_ew(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, c
   // tile space in 256-row blocks; rasterisation group halves accordingly
   p.m_blocks = cdiv(p.M, 256);
   p.group_m = p.group_m > 1 ? (p.group_m + 1) / 2 : 1;
+  static const int dbg_gm = dbg_env("DDNN_DBG_GROUP_M"), dbg_pairs = dbg_env("DDNN_DBG_PAIRS");
+  if (dbg_gm > 0) p.group_m = dbg_gm;
   if (p.group_m > p.m_blocks) p.group_m = p.m_blocks;
   const int total = p.m_blocks * p.n_blocks * p.splits;
   int pairs = (num_sms() - g_sm_reserve.load()) / 2;
+  if (dbg_pairs > 0 && dbg_pairs < pairs) pairs = dbg_pairs;
   if (pairs < 1) pairs = 1;
   if (pairs > total) pairs = total;
   cudaLaunchConfig_t cfg{};

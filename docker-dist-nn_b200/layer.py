@@ -386,16 +386,47 @@ class Layer:
                                   signals=sig)
         return dst
 
-    def step(self, lr: float, rows: Optional[int] = None) -> None:
+    def step(self, lr: float, rows: Optional[int] = None, chunk_rows: Optional[int] = None) -> None:
         """dW = A^T.dZ over the first ``rows`` buffered rows with the SGD update fused into the
-        GEMM epilogue: W -= lr*dW, b -= lr*db, bf16 shadow refreshed."""
+        GEMM epilogue: W -= lr*dW, b -= lr*db, bf16 shadow refreshed.  With ``chunk_rows`` (< rows) the
+        reduction is cut into row chunks accumulated in fp32 (``accumulate_grads``) and applied once."""
         rows = self._rows if rows is None else rows
+        if chunk_rows and chunk_rows < rows:
+            for r0 in range(0, rows, chunk_rows):
+                self.accumulate_grads(r0, min(rows, r0 + chunk_rows), first=(r0 == 0))
+            self.apply_update(lr)
+            return
         b = self._bufs
         for i, p in enumerate(self.layer_params):
             k_, n_ = p["weights"].shape
             with self._span(f"dW+SGD L{i + 1} {k_}x{n_}"):
                 ops.dense_backward_dw_sgd(self._a(i)[:rows], b["dz"][i][:rows], p["weights"], p["biases"], lr,
                                           w_shadow=self._shadow[i], workspace=self._ws)
+
+    def accumulate_grads(self, row0: int, row1: int, first: bool) -> None:
+        """Adds the weight / bias gradients of rows [row0, row1) of every local layer to the node's fp32
+        accumulators (``first`` overwrites them); weights stay untouched until ``apply_update``.  A pipeline stage
+        calls this for the micro-batches it has finished while it waits for its neighbours; a very long batch is
+        cut into such chunks so that the operands of each GEMM stay in L2.  The chunk boundaries are part of the
+        arithmetic (fp32 rounding of the partial sums)."""
+        b = self._bufs
+        if "gw" not in b:
+            b["gw"] = [torch.empty_like(p["weights"]) for p in self.layer_params]
+            b["gb"] = [torch.empty_like(p["biases"]) for p in self.layer_params]
+        sl = slice(row0, row1)
+        for i, p in enumerate(self.layer_params):
+            k_, n_ = p["weights"].shape
+            with self._span(f"dW chunk L{i + 1} {k_}x{n_}"):
+                ops.dense_backward_dw_accumulate(self._a(i)[sl], b["dz"][i][sl], b["gw"][i], b["gb"][i], first,
+                                                 workspace=self._ws)
+
+    def apply_update(self, lr: float) -> None:
+        """W -= lr * dW, b -= lr * db from the accumulators of ``accumulate_grads``; bf16 shadow refreshed."""
+        b = self._bufs
+        for i, p in enumerate(self.layer_params):
+            k_, n_ = p["weights"].shape
+            with self._span(f"SGD apply L{i + 1} {k_}x{n_}"):
+                ops.sgd_apply(p["weights"], p["biases"], b["gw"][i], b["gb"][i], lr, w_shadow=self._shadow[i])
 
     def backward_and_step(self, lr: float, rows: Optional[int] = None, side: Optional[torch.cuda.Stream] = None,
                           top: Optional[int] = None) -> None:

@@ -166,6 +166,35 @@ def dense_backward_dw_sgd(x: torch.Tensor, dz: torch.Tensor, w_master: torch.Ten
                                              1, b, k, n, _DT[x.dtype], _p(ws), ws.numel(), _stream(x)))
 
 
+def dense_backward_dw_accumulate(x: torch.Tensor, dz: torch.Tensor, dw_acc: torch.Tensor, db_acc: torch.Tensor,
+                                 first: bool, workspace: Optional[torch.Tensor] = None) -> None:
+    """dw_acc (+)= x.T @ dz ; db_acc (+)= colsum(dz) for one row chunk of the batch (``first`` overwrites)."""
+    _req(x, name="x"); _req(dz, x.dtype, "dz"); _req(dw_acc, torch.float32, "dw_acc"); _req(db_acc, torch.float32, "db_acc")
+    b, k = x.shape
+    n = dz.shape[1]
+    if tuple(dw_acc.shape) != (k, n) or db_acc.numel() != n or dz.shape[0] != b:
+        raise ValueError("dense_backward_dw_accumulate: shape mismatch")
+    ws = _workspace(workspace, b, k, n, x)
+    with torch.cuda.device(x.device):
+        check(lib.ddnn_dense_backward_dw_accumulate(_p(x), _p(dz), _p(dw_acc), _p(db_acc), 1 if first else 0, b, k, n,
+                                                    _DT[x.dtype], _p(ws), ws.numel(), _stream(x)))
+
+
+def sgd_apply(w_master: torch.Tensor, bias: torch.Tensor, dw: torch.Tensor, db: torch.Tensor, lr: float,
+              w_shadow: Optional[torch.Tensor] = None) -> None:
+    """w_master -= lr * dw ; bias -= lr * db ; shadow = bf16(w_master): the update after the last gradient chunk."""
+    _req(w_master, torch.float32, "w_master"); _req(bias, torch.float32, "bias")
+    _req(dw, torch.float32, "dw"); _req(db, torch.float32, "db")
+    if w_shadow is not None:
+        _req(w_shadow, torch.bfloat16, "w_shadow")
+    k, n = w_master.shape
+    if tuple(dw.shape) != (k, n) or db.numel() != n or bias.numel() != n:
+        raise ValueError("sgd_apply: shape mismatch")
+    with torch.cuda.device(w_master.device):
+        check(lib.ddnn_sgd_apply(_p(w_master), _p(w_shadow), _p(bias), _p(dw), _p(db), float(lr), k, n,
+                                 _stream(w_master)))
+
+
 def output_layer_supported(a: torch.Tensor, k: int, n: int) -> bool:
     """Shapes the fused output-layer step handles (ddnn_output_layer_train): N <= 16, K <= 256, rows of
     the input 16-byte aligned and at most 64 16-byte chunks long."""

@@ -122,6 +122,25 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ,
 size_t ddnn_dw_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype);
 
 /*
+ * The weight gradient of one ROW CHUNK of the batch, accumulated in caller-owned fp32 buffers:
+ *   first != 0 :  dW_acc  = X^T . dZ ;  db_acc  = column sums of dZ
+ *   first == 0 :  dW_acc += X^T . dZ ;  db_acc += column sums of dZ      (one fp32 rounding per element and call)
+ * followed, after the last chunk, by ddnn_sgd_apply:  W_master -= lr * dW_acc ; bias -= lr * db_acc ; W_shadow =
+ * bf16(W_master) if given.  Same kernels, workspace rule and determinism as ddnn_dense_backward_dw_sgd (the
+ * accumulation is its update epilogue with the accumulator in W_master's place).  Two uses: a pipeline stage
+ * computes the gradient of the micro-batches it has finished while it waits for its neighbours (zero-bubble
+ * order), and a reduction over a very long batch is cut into chunks whose operands stay in L2 (the 16384 x 16384
+ * x 65536 GEMM in one piece re-reads its operands from HBM 25 times over).  The chunking is part of the
+ * arithmetic: results are bit-identical for equal chunk boundaries, and differ from the one-piece GEMM by fp32
+ * rounding of the partial sums.  No reference counterpart (grpc_node.py has no backward pass).
+ */
+int ddnn_dense_backward_dw_accumulate(const void* X, const void* dZ, float* dW_acc, float* db_acc, int first,
+                                      int64_t B, int64_t K, int64_t N, int dtype,
+                                      void* workspace, size_t workspace_bytes, void* stream);
+int ddnn_sgd_apply(float* W_master, void* W_shadow, float* bias, const float* dW, const float* db, float lr,
+                   int64_t K, int64_t N, void* stream);
+
+/*
  * Same computation and arguments as ddnn_dense_backward_dw_sgd, minus the workspace: the
  * split-K scratch is an array built into the library (DDNN_STATIC_SCRATCH_BYTES per GPU, held
  * from module load to process exit).  This entry point has no counterpart in the reference.

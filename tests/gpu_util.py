@@ -28,6 +28,17 @@ BF16_ACT_TOL = 2e-2
 BF16_GRAD_TOL = 3e-2
 
 
+def bf16_update_tol(rows: int, below_relu: bool) -> float:
+    """Bound (normalised max error) on a weight UPDATE of the bf16 path against the float64 oracle.  Rounding
+    alone (operands to bf16, eps = 2^-9 each, fp32 accumulation) stays within BF16_GRAD_TOL.  A layer BELOW a ReLU
+    has a second, larger term: the bf16 forward error (~2e-3 of a pre-activation at K = 8192) flips the gates of
+    pre-activations that close to zero, and a flipped gate adds or removes ONE whole term x * dz of the ``rows``-term
+    sum behind each element of dW.  The largest such term is ~5 sigma(dz) * max(x) while max |dW| over the matrix
+    is ~5.5 * sqrt(rows) * rms(x) * sigma(dz), i.e. the error is <= ~1.6 / sqrt(rows) of the tensor's maximum
+    (9% at 300 rows, 0.6% at 65536): 2 / sqrt(rows) is allowed for it."""
+    return BF16_GRAD_TOL + (2.0 / float(rows) ** 0.5 if below_relu else 0.0)
+
+
 def elementwise_ok(got, ref, rtol: float, atol: float) -> bool:
     """Elementwise check beside the normalised-max one: |got - ref| <= rtol * |ref| + atol for EVERY element, so
     an element far below the tensor's maximum cannot hide a large relative error behind it.  ``atol`` is stated

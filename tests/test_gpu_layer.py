@@ -9,7 +9,7 @@ import torch
 
 import oracle
 from ddnn_b200.config import make_params, synthetic_batch
-from gpu_util import BF16_ACT_TOL, F32_TOL, rel_err, to_dev, to_np
+from gpu_util import BF16_ACT_TOL, F32_TOL, bf16_update_tol, rel_err, to_dev, to_np
 
 pytestmark = pytest.mark.gpu
 
@@ -388,11 +388,13 @@ def test_narrow_configuration_tracks_oracle_at_full_size(cuda_device):
         got = t.train_step(xd, yd, lr).item()
         want = oracle.train_step(ref, x, y, lr)
         assert abs(got - want) < 2e-2 * want
-    for g, r, b0 in zip(t.export_params(), ref, before):
+    for i, (g, r, b0) in enumerate(zip(t.export_params(), ref, before)):
         assert rel_err(g["weights"], r["weights"]) < BF16_ACT_TOL
-        # the UPDATE itself (difference to the initial weights), not just the weights it barely moves
-        assert rel_err(g["weights"] - b0["weights"], r["weights"] - b0["weights"]) < 0.1
-        assert rel_err(g["biases"] - b0["biases"], r["biases"] - b0["biases"]) < 0.1
+        # the UPDATE itself (difference to the initial weights), not just the weights it barely moves: bound from
+        # bf16 rounding plus, below a ReLU, gate flips (gpu_util.bf16_update_tol; two steps are compared, so twice)
+        tol = 2 * bf16_update_tol(65536, below_relu=(i < 2))
+        assert rel_err(g["weights"] - b0["weights"], r["weights"] - b0["weights"]) < tol, i
+        assert rel_err(g["biases"] - b0["biases"], r["biases"] - b0["biases"]) < tol, i
 
 
 @pytest.mark.parametrize("dtype,dims,cap,tail", [("f32", [784, 128, 64, 10], 4096, 3540),

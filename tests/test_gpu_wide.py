@@ -11,7 +11,7 @@ import pytest
 import torch
 
 import oracle
-from gpu_util import BF16_ACT_TOL, BF16_GRAD_TOL, elementwise_ok, rel_err, to_np
+from gpu_util import BF16_ACT_TOL, BF16_GRAD_TOL, bf16_update_tol, elementwise_ok, rel_err, to_np
 
 pytestmark = pytest.mark.gpu
 
@@ -106,7 +106,7 @@ def test_softmax_ce_at_full_width(cuda_device, width):
 def test_train_step_of_an_8192_wide_net(cuda_device):
     """One full Trainer step (forward, softmax-CE over 8192 classes, dX, dW + SGD) of a 2-layer 8192-wide bf16 net,
     300 rows, against oracle.train_step in float64 from the same fp32 weights: loss, post-step weights, and the
-    UPDATE itself within the bf16 gradient bound (BF16_GRAD_TOL, derived in gpu_util.py)."""
+    UPDATE itself within the bf16 update bound (bf16_update_tol in gpu_util.py: rounding + ReLU gate flips)."""
     from ddnn_b200 import Trainer
     width, rows, lr = 8192, 300, 0.5
     g = torch.Generator(device="cuda").manual_seed(7)
@@ -122,7 +122,8 @@ def test_train_step_of_an_8192_wide_net(cuda_device):
     got = t.train_step(x, y, lr).item()
     want = oracle.train_step(ref, to_np(x), y.cpu().numpy().astype(np.int64), lr)
     assert abs(got - want) < 2e-2 * want
-    for p, r, b0 in zip(t.layer.layer_params, ref, before):
+    for i, (p, r, b0) in enumerate(zip(t.layer.layer_params, ref, before)):
         gw = to_np(p["weights"])
         assert rel_err(gw, r["weights"]) < BF16_ACT_TOL
-        assert rel_err(gw - b0, r["weights"] - b0) < BF16_GRAD_TOL
+        # layer 1 sits below a ReLU (gate flips, see bf16_update_tol); the output layer's dZ has no gate above it
+        assert rel_err(gw - b0, r["weights"] - b0) < bf16_update_tol(rows, below_relu=(i == 0)), i

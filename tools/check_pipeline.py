@@ -15,12 +15,13 @@ from ddnn_b200.config import make_params, synthetic_batch  # noqa: E402
 from ddnn_b200.pipeline import PipelineStage, stage_assignment  # noqa: E402
 
 
-def run(transport, dims, acts, dtype, rows, micro, steps, rank, world, device):
+def run(transport, dims, acts, dtype, rows, micro, steps, rank, world, device, schedule="gpipe", dw_chunk=None):
     params = make_params(dims, acts, seed=3)
     lo, hi = stage_assignment(len(acts), world)[rank]
     layer = Layer.from_params(params[lo:hi], dims[lo], dtype=dtype, device=device,
                               input_activation=(acts[lo - 1] if lo > 0 else "linear"), is_output=(hi == len(acts)))
-    stage = PipelineStage(layer, rank, world, transport=transport)
+    stage = PipelineStage(layer, rank, world, transport=transport, schedule=schedule, dw_chunk=dw_chunk,
+                          layers_per_stage=[b - a for a, b in stage_assignment(len(acts), world)])
     losses = []
     for s in range(steps):
         x, y = synthetic_batch(rows, dims[0], dims[-1], seed=s)
@@ -47,6 +48,13 @@ def main():
         w_n, l_n, (lo, hi) = run("nccl", dims, acts, dtype, rows, micro, 4, rank, world, device)
         w_p, l_p, _ = run("peer", dims, acts, dtype, rows, micro, 4, rank, world, device)
         same = all(torch.equal(a, b) for a, b in zip(w_n, w_p)) and l_n == l_p
+        # chunked weight gradients: the GPipe and the zero-bubble order must agree bit for bit (same chunk boundaries),
+        # over NCCL as over peer memory, and stay within rounding of the one-piece gradient
+        w_c, l_c, _ = run("nccl", dims, acts, dtype, rows, micro, 4, rank, world, device, "gpipe", 2)
+        w_z, l_z, _ = run("peer", dims, acts, dtype, rows, micro, 4, rank, world, device, "zb", 2)
+        same = same and all(torch.equal(a, b) for a, b in zip(w_c, w_z)) and l_c == l_z
+        chunk_err = max(float((a - b).abs().max() / (b.abs().max() + 1e-30)) for a, b in zip(w_z, w_p))
+        same = same and chunk_err < 1e-5
         # single-GPU reference of the same steps (every rank computes it; cheap)
         tr = Trainer(make_params(dims, acts, seed=3), dtype=dtype, device=device)
         ref_l = []

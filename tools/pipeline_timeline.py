@@ -43,7 +43,9 @@ def main():
     layer = Layer.from_params(params, dims[lo], dtype=dtype, device=dev, container_name=f"stage{rank}",
                               input_activation=(acts[lo - 1] if lo > 0 else "linear"), is_output=(hi == n_layers))
     stage = PipelineStage(layer, rank, world, transport=os.environ.get("DDNN_TRANSPORT", "peer") if world > 1 else "nccl",
-                          schedule=os.environ.get("DDNN_SCHEDULE", "gpipe"))
+                          schedule=os.environ.get("DDNN_SCHEDULE", "gpipe"),
+                          dw_chunk=int(os.environ.get("DDNN_DW_CHUNK", "0")) or None,
+                          layers_per_stage=[b - a for a, b in stage_assignment(n_layers, world)])
     x = torch.rand((rows, dims[0]), device=dev, generator=torch.Generator(device=dev).manual_seed(0)).to(torch.bfloat16) \
         if rank == 0 else None
     y = torch.randint(0, dims[-1], (rows,), device=dev, generator=torch.Generator(device=dev).manual_seed(2),
@@ -74,14 +76,15 @@ def main():
     barrier()
     spans, layer._probe = layer._probe, None
     rows_out = [(name, start.elapsed_time(a), a.elapsed_time(b)) for name, a, b in spans]
-    with open(f"{out}_{workload}_n{world}_rank{rank}.csv", "w") as f:
+    tag = os.environ.get("DDNN_SCHEDULE", "gpipe") + (f"_chunk{os.environ['DDNN_DW_CHUNK']}" if os.environ.get("DDNN_DW_CHUNK") else "")
+    with open(f"{out}_{workload}_{tag}_n{world}_rank{rank}.csv", "w") as f:
         f.write("name,start_ms,dur_ms\n")
         for name, s, d in rows_out:
             f.write(f"{name},{s:.4f},{d:.4f}\n")
     busy = sum(d for _, _, d in rows_out)
     fwd = [r for r in rows_out if r[0].startswith("forward")]
     bwd = [r for r in rows_out if r[0].startswith("dX") or r[0].startswith("softmax")]
-    upd = [r for r in rows_out if r[0].startswith("dW")]
+    upd = [r for r in rows_out if r[0].startswith("dW") or r[0].startswith("SGD")]
 
     def phase(rs):
         if not rs:

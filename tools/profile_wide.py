@@ -24,6 +24,12 @@ def main():
     out = torch.empty((mb, width), dtype=torch.bfloat16, device=dev)
     ws = torch.empty((max(256, ops.dw_workspace_bytes(rows, width, width, torch.bfloat16)),), dtype=torch.uint8, device=dev)
     reps = int(os.environ.get("REPS", "2"))
+    chunk = int(os.environ.get("DW_CHUNK", "0"))  # > 0: only the dW GEMM, over the first DW_CHUNK rows (ncu experiments)
+    if chunk:
+        for _ in range(reps):
+            ops.dense_backward_dw_sgd(x[:chunk], dz[:chunk], wm, bias, 0.0, w_shadow=w, workspace=ws)
+        torch.cuda.synchronize()
+        return
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
     for r in range(reps):  # the last repetition is the one ncu keeps (-s skips the first)
         ev[0].record()
