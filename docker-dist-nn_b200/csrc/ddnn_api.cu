@@ -417,12 +417,7 @@ int ddnn_sgd_apply(float* W_master, void* W_shadow, float* bias, const float* dW
     set_error("ddnn_sgd_apply: null pointer");
     return DDNN_ERR_ARG;
   }
-  if (N % 4 != 0) {  // the reducer reads gradient rows at a pitch of N rounded up to 4
-    set_error("ddnn_sgd_apply: N = %lld is not a multiple of 4", (long long)N);
-    return DDNN_ERR_UNSUPPORTED;
-  }
-  // a one-split "reduction": W -= lr * dW, bias -= lr * db, shadow refreshed, in one launch
-  return reduce_dw(dW, db, 1, K, N, W_master, W_shadow, bias, nullptr, nullptr, lr, 1, (cudaStream_t)stream);
+  return sgd_apply(W_master, W_shadow, bias, dW, db, lr, K, N, (cudaStream_t)stream);
 }
 
 size_t ddnn_output_layer_workspace_bytes(int64_t B, int64_t K, int64_t N, int dtype) {

@@ -44,6 +44,9 @@ int reduce_dw(const float* dw_part, const float* db_part, int splits, int64_t K,
 int reduce_dw2(const float* dw_part, const float* db_part, int splits, int splits_b, int64_t K, int64_t N,
                float* W_master, void* W_shadow, float* bias, float* dW_out, float* db_out, float lr,
                int apply, cudaStream_t st);
+// W -= lr * G, bias -= lr * gb, shadow = bf16(W) (any N): the update after chunked gradient accumulation
+int sgd_apply(float* W, void* W_shadow, float* bias, const float* G, const float* gb, float lr, int64_t K, int64_t N,
+              cudaStream_t st);
 // db partials from dZ alone (used by the tcgen05 path): db_part[z][Np]
 int colsum_partials(const void* dZ, float* db_part, int splits, int64_t B, int64_t N, int dtype,
                     cudaStream_t st);

@@ -155,6 +155,33 @@ colsum_bf16x8_kernel(const bf16* __restrict__ dZ, float* __restrict__ part, int6
   }
 }
 
+// W -= lr * G (and the bf16 shadow), bias -= lr * gb: the update after the last gradient chunk.  Flat over the
+// K*N elements (any N); 16-byte accesses when every pointer allows it.
+__global__ void __launch_bounds__(256)
+sgd_apply_kernel(float* __restrict__ W, bf16* __restrict__ shadow, float* __restrict__ bias, const float* __restrict__ G,
+                 const float* __restrict__ gb, float lr, int64_t total, int N, bool vec) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (vec) {
+    for (int64_t i = tid * 4; i < total; i += stride * 4) {
+      float4 w = ld4(W + i);
+      const float4 g = ld4(G + i);
+      w.x -= lr * g.x; w.y -= lr * g.y; w.z -= lr * g.z; w.w -= lr * g.w;
+      st4(W + i, w);
+      if (shadow) st4(shadow + i, w);
+    }
+  } else {
+    for (int64_t i = tid; i < total; i += stride) {
+      const float w = W[i] - lr * G[i];
+      W[i] = w;
+      if (shadow) shadow[i] = __float2bfloat16_rn(w);
+    }
+  }
+  for (int64_t i = tid; i < N; i += stride) bias[i] -= lr * gb[i];
+}
+
 template <typename T>
 bool vec_ok(const T* p, int64_t ld) {
   return p && (ld % 4 == 0) && ((reinterpret_cast<uintptr_t>(p) % (4 * sizeof(T))) == 0);
@@ -201,6 +228,20 @@ int reduce_dw2(const float* dw_part, const float* db_part, int splits, int split
     else DDNN_REDUCE(32, EpiStoreF32, EpiStoreF32, ew, eb, vw, vb);
   }
 #undef DDNN_REDUCE
+  count_launch();
+  return DDNN_OK;
+}
+
+int sgd_apply(float* W, void* W_shadow, float* bias, const float* G, const float* gb, float lr, int64_t K, int64_t N,
+              cudaStream_t st) {
+  const int64_t total = K * N;
+  const bool vec = total % 4 == 0 && reinterpret_cast<uintptr_t>(W) % 16 == 0 && reinterpret_cast<uintptr_t>(G) % 16 == 0 &&
+                   (!W_shadow || reinterpret_cast<uintptr_t>(W_shadow) % 8 == 0);
+  long blocks = (long)((total / (vec ? 4 : 1) + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  DDNN_CUDA_CHECK(launch_pdl(sgd_apply_kernel, dim3((unsigned)blocks), dim3(256), 0, st, W, (bf16*)W_shadow, bias, G, gb,
+                             lr, total, (int)N, vec));
   count_launch();
   return DDNN_OK;
 }

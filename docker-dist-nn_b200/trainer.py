@@ -97,6 +97,34 @@ class Trainer:
     def static_inputs(self) -> Tuple[torch.Tensor, torch.Tensor]:
         return self._static[0], self._static[1]
 
+    def train_step_replicas(self, x: torch.Tensor, labels: torch.Tensor, lr: Optional[float] = None, group=None
+                            ) -> torch.Tensor:
+        """Data-parallel step (the reference has no replicated parameters): every rank of
+        ``group`` holds a full replica and calls this with ITS rows of the global batch.  Each replica runs
+        forward / softmax-CE / dX on its rows with the loss scaled by the GLOBAL row count, accumulates dW / db in
+        fp32 (``Layer.accumulate_grads``), the accumulators are summed over the ranks (one all-reduce per layer:
+        NCCL on GPUs), and every rank applies the same update -- the result is the full-batch step of the
+        concatenated batch up to fp32 summation order.  Returns the global mean loss (device scalar)."""
+        import torch.distributed as dist
+        L = self.layer
+        lr = self.lr if lr is None else lr
+        rows = x.shape[0]
+        total = torch.tensor([rows], dtype=torch.int64, device=self.device)
+        dist.all_reduce(total, group=group)
+        denom = int(total.item())
+        L.begin_batch(rows)
+        L.forward_train(x, 0)
+        loss = L.loss_and_grad(labels, 0, denom=denom)
+        L.backward(0, rows, need_input_grad=False)
+        L.accumulate_grads(0, rows, first=True)
+        b = L._bufs
+        for gw, gb in zip(b["gw"], b["gb"]):
+            dist.all_reduce(gw, group=group)
+            dist.all_reduce(gb, group=group)
+        dist.all_reduce(loss, group=group)
+        L.apply_update(lr)
+        return loss
+
     # ------------------------------------------------------------------ end-to-end host calls
     def train_step_host(self, x_host: torch.Tensor, y_host: torch.Tensor, lr: Optional[float] = None) -> float:
         """One synchronous step from HOST data: x_host (B, in) fp32 and y_host (B,) int32 in

@@ -444,3 +444,33 @@ def test_input_batch_is_read_in_place(cuda_device, dtype, dims):
         assert l_in == l_cp
     for a, b in zip(t_in.export_params(), t_cp.export_params()):
         assert np.array_equal(a["weights"], b["weights"]) and np.array_equal(a["biases"], b["biases"])
+
+
+@pytest.mark.parametrize("dtype,dims,rows,chunk", [("f32", [784, 128, 64, 10], 1000, 384),
+                                                   ("bf16", [512, 512, 256, 64], 4096, 1024)])
+def test_chunked_weight_gradient_and_update(cuda_device, dtype, dims, rows, chunk):
+    """ddnn_dense_backward_dw_accumulate + ddnn_sgd_apply (Layer.step(chunk_rows=...)): the gradient summed over row
+    chunks (ragged last chunk) and applied once equals the one-piece fused update up to fp32 rounding of the
+    partial sums, is bit-reproducible, and tracks the float64 oracle."""
+    from ddnn_b200 import Trainer
+    acts = ["relu", "sigmoid", "softmax"]
+    x, y = synthetic_batch(rows, dims[0], dims[-1], seed=11)
+    xd, yd = to_dev(x), to_dev(y, torch.int32)
+    ref = [dict(p) for p in make_params(dims, acts, seed=4)]
+    want = oracle.train_step(ref, x, y, 0.1)
+    outs = []
+    for chunk_rows in (None, chunk, chunk):
+        t = Trainer(make_params(dims, acts, seed=4), dtype=dtype)
+        L = t.layer
+        L.begin_batch(rows)
+        L.forward_train(xd, 0)
+        got = L.loss_and_grad(yd, 0).item()
+        L.backward(0, rows, need_input_grad=False)
+        L.step(0.1, rows, chunk_rows=chunk_rows)
+        assert abs(got - want) < (F32_TOL if dtype == "f32" else 2e-2) * want
+        outs.append(t.export_params())
+    one_piece, chunked, again = outs
+    for a, b, c, r in zip(one_piece, chunked, again, ref):
+        assert np.array_equal(b["weights"], c["weights"]) and np.array_equal(b["biases"], c["biases"])
+        assert rel_err(b["weights"], a["weights"]) < 1e-6 and rel_err(b["biases"], a["biases"]) < 1e-6
+        assert rel_err(b["weights"], r["weights"]) < (F32_TOL if dtype == "f32" else BF16_ACT_TOL)

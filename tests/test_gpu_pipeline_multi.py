@@ -50,3 +50,13 @@ def test_eval_driver_over_the_pipeline(tmp_path):
     m = re.search(r"Correct predictions: (\d+) out of (\d+)", r.stdout)
     assert m and int(m.group(2)) == 300 and int(m.group(1)) == want, r.stdout[-3000:]
     assert "Batch 3/3 completed" in r.stdout
+
+
+@pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_data_parallel_replicas_match_the_full_batch_step():
+    """tools/check_replicas.py: Trainer.train_step_replicas (dW / db accumulators all-reduced over NCCL, one update)
+    on 2 shards of a batch = the single-GPU step on the whole batch, and the replicas stay bit-identical."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr",
+           "127.0.0.1", "--master-port", "29735", os.path.join(REPO, "tools", "check_replicas.py")]
+    r = subprocess.run(cmd, cwd=REPO, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    assert r.returncode == 0 and "REPLICA CHECK PASS" in r.stdout, r.stdout[-3000:]
