@@ -39,6 +39,7 @@ SYMBOLS = {
     "ddnn_set_f32_tensor_cores": (C.c_int, [_i32]),
     "ddnn_set_cta_pairs": (C.c_int, [_i32]),
     "ddnn_set_pdl": (C.c_int, [_i32]),
+    "ddnn_set_cluster_split_k": (C.c_int, [_i32]),
     "ddnn_dense_forward": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32, _vp]),
     "ddnn_dense_forward_signalled": (C.c_int, [_vp, _vp, _vp, _vp, _i64, _i64, _i64, _i32, _i32, _i32,
                                                C.POINTER(Signals), _vp]),

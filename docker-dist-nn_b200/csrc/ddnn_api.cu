@@ -128,6 +128,11 @@ int ddnn_set_f32_tensor_cores(int mode) {
   return DDNN_OK;
 }
 
+int ddnn_set_cluster_split_k(int on) {
+  tf32_set_cluster_dw(on);
+  return DDNN_OK;
+}
+
 int ddnn_set_sm_reserve(int sms) {
   if (sms < 0 || sms > 64) {
     set_error("ddnn_set_sm_reserve: %d is out of range [0, 64]", sms);
@@ -371,6 +376,9 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
     return reduce_dw(dw_part, db_part, cs, K, N, W_master, W_shadow, bias, dW_out, db_out, lr, apply, st);
   }
   if (use_tf32(dtype, B, K, N, 0, {X, dZ, W_master, dW_out})) {
+    int taken = 0;  // split-K reduced inside the kernel across a thread-block cluster: one launch, no partials in HBM
+    rc = tf32_dw_cluster((const float*)X, (const float*)dZ, W_master, bias, dW_out, db_out, lr, apply, B, K, N, &taken, st);
+    if (rc || taken) return rc;
     const int splits = tf32_dw_splits(B, K, N);
     int cs = colsum_splits(B, N), db_fused = 0;
     float* dw_part = ws;

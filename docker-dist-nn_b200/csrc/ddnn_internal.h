@@ -103,4 +103,10 @@ int tf32_dw_splits(int64_t B, int64_t K, int64_t N);
 int tf32_dw_partials(const float* X, const float* dZ, float* dw_part, int splits, int64_t B, int64_t K,
                      int64_t N, float* db_part, int* db_fused, cudaStream_t st);
 
+// dW + db + SGD (or gradient store) in one launch: split-K over a thread-block cluster, reduced through distributed
+// shared memory.  *taken = 0: no cluster plan for this shape, run tf32_dw_partials + reduce_dw2 instead.
+int tf32_dw_cluster(const float* X, const float* dZ, float* W_master, float* bias, float* dW_out, float* db_out, float lr,
+                    int apply, int64_t B, int64_t K, int64_t N, int* taken, cudaStream_t st);
+void tf32_set_cluster_dw(int on);
+
 }  // namespace ddnn

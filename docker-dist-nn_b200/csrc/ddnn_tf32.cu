@@ -19,6 +19,10 @@
 // Same three operand layouts as the bf16 family (descriptor major-ness instead of transposes in memory).
 #include <cuda.h>
 
+#include <map>
+#include <mutex>
+#include <tuple>
+
 #include "ddnn_umma.cuh"
 
 namespace ddnn {
@@ -36,7 +40,27 @@ struct Tf32Params {
   int64_t zrows;  // row offset per split (split-K partials)
   float* db_part;  // dW split-K with one tile per CTA: column sums of the B operand, [split][db_np] (else null)
   int db_np;
+  // Cluster split-K (template flag CL): the `splits` CTAs of a thread-block cluster own ONE output tile, each reduces
+  // its share of the batch, and the partial tiles are summed through distributed shared memory -- no partials in
+  // HBM, no reducer launch.  The CTAs then apply the epilogue themselves: SGD on W / bias (apply) or fp32 store.
+  float* cl_w;      // apply: W_master (updated in place); else: dW_out
+  float* cl_b;      // apply: bias; else: db_out
+  float cl_lr;
+  int cl_apply;
 };
+
+constexpr int CL_PITCH_PAD = 4;  // floats of padding per partial-tile row (keeps float4 alignment, spreads the banks)
+
+__device__ __forceinline__ float4 ld_dsmem4(uint32_t local_addr, uint32_t cta) {
+  uint32_t ra;
+  float4 v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(cta));
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(ra)
+               : "memory");
+  return v;
+}
 
 __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
                                           uint32_t accum) {
@@ -146,11 +170,12 @@ __device__ __forceinline__ void tf32_epilogue(const Epi& epi, int M, int N, floa
   }
 }
 
-template <bool A_MN, bool B_MN, int BN, typename Epi>
+template <bool A_MN, bool B_MN, int BN, typename Epi, bool CL = false>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const Tf32Params p, const Epi epi) {
   using C = TCfg<BN>;
+  static_assert(!CL || (A_MN && B_MN), "cluster split-K is the dW layout");
   constexpr int NACC = (A_MN && B_MN) ? 1 : C::NACC_FWD;  // accumulator sets per tile (see TCfg)
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -168,6 +193,10 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int total_tiles = p.m_blocks * p.n_blocks * p.splits;
+  // CL: one (tile, split) per CTA; the CTAs of a cluster (consecutive blockIdx.x) share the tile and differ in the split
+  const uint32_t cl_rank = CL ? cluster_ctarank() : 0u;
+  const int tile_first = CL ? (int)cl_rank * (p.m_blocks * p.n_blocks) + (int)(blockIdx.x / p.splits) : (int)blockIdx.x;
+  const int tile_step = CL ? total_tiles : (int)gridDim.x;
   pdl_launch_dependents();  // the next kernel of the stream may set up while this one runs
 
   if (warp == 0 && lane == 0) {
@@ -195,7 +224,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   // from the dZ tiles already in shared memory.  All-ones is layout-invariant, so 1 KB (one k-step of one 32-wide
   // MN atom) stands for the whole 128 x 32 operand: LBO = 0 aliases the MN atoms, the descriptor never advances.
   const uint32_t ones_base = (bars + C::BAR_BYTES + C::STG_BYTES + 127u) & ~127u;
-  const bool fuse_db = A_MN && B_MN && p.db_part != nullptr;
+  const bool fuse_db = A_MN && B_MN && (CL || p.db_part != nullptr);
   if (fuse_db && warp == 3) {
     float* o = reinterpret_cast<float*>(smem_raw + (ones_base - raw));
     for (int i = lane; i < (int)(C::ONES_BYTES / 4); i += 32) o[i] = 1.0f;
@@ -211,7 +240,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     // ===================== TMA producer =====================
     if (lane == 0) {
       uint32_t stage = 0, phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = tile_first; tile < total_tiles; tile += tile_step) {
         const TileCoord t = decode_tile(tile, p);
         for (int kb = t.kb0; kb < t.kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
@@ -248,7 +277,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const uint64_t desc_al = tf32_desc<A_MN>(lo_ring, 0);                 // A lo of slot 0
       const uint64_t ones_desc = make_desc_layout(ones_base, 0, 512, 1u);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0, u = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = tile_first; tile < total_tiles; tile += tile_step) {
         const TileCoord t = decode_tile(tile, p);
         mbar_wait(tempty_bar(as), aphase ^ 1);
         tc_fence_after();
@@ -289,7 +318,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     constexpr int PER = (A_CH + B_CH + CONV_THREADS - 1) / CONV_THREADS;
     static_assert(A_CH % CONV_THREADS == 0, "a thread's j-th chunk is in A or in B for all threads alike");
     uint32_t stage = 0, phase = 0, u = 0, uphase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = tile_first; tile < total_tiles; tile += tile_step) {
       const TileCoord t = decode_tile(tile, p);
       for (int kb = t.kb0; kb < t.kb1; ++kb) {
         mbar_wait(full_bar(stage), phase);
@@ -333,15 +362,49 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     const int q = warp & 3;
     float* stg = reinterpret_cast<float*>(smem_raw + (bars + C::BAR_BYTES - raw)) + q * 32 * C::STG_PITCH;
     uint32_t as = 0, aphase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    for (int tile = tile_first; tile < total_tiles; tile += tile_step) {
       const TileCoord t = decode_tile(tile, p);
       mbar_wait(tfull_bar(as), aphase);
       tc_fence_after();
       const uint32_t d_main = tmem_base + as * (NACC * 2 * BN);
+      if (CL) {
+        // the partial tile (main + correction) goes to shared memory, over the operand ring: every MMA that read the
+        // ring has retired (tfull), and this CTA loads nothing more
+        float* part = reinterpret_cast<float*>(smem_raw + (tiles - raw));
+        constexpr int PITCH = BN + CL_PITCH_PAD;
+        const int row = q * 32 + lane;
+#pragma unroll 1
+        for (int c = 0; c < BN / 32; ++c) {
+          float v[32], w[32];
+          tmem_ld32(d_main + c * 32 + ((uint32_t)(q * 32) << 16), v);
+          tmem_ld32(d_main + BN + c * 32 + ((uint32_t)(q * 32) << 16), w);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(&part[row * PITCH + c * 32 + 4 * j]) =
+                make_float4(v[4 * j] + w[4 * j], v[4 * j + 1] + w[4 * j + 1], v[4 * j + 2] + w[4 * j + 2],
+                            v[4 * j + 3] + w[4 * j + 3]);
+        }
+        if (t.m_blk == 0 && q == 0) {  // bias-gradient partial: TMEM lane 0 of the ones-accumulators
+          float* dbp = part + BLOCK_M * PITCH;
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            float v[32], w[32];
+            tmem_ld32(tmem_base + 2 * BN + c * 32, v);
+            tmem_ld32(tmem_base + 3 * BN + c * 32, w);
+            tmem_ld_wait();
+            if (lane == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) dbp[c * 32 + j] = v[j] + w[j];
+            }
+          }
+        }
+      } else {
       tf32_epilogue<BN, Epi>(epi, p.M, p.N, stg, d_main, d_main + BN, min(NACC, t.kb1 - t.kb0),
                              t.m_blk * BLOCK_M + q * 32, t.n_blk * BN,
                              (int64_t)t.ks * p.zrows, q, lane);
-      if (fuse_db && t.m_blk == 0 && q == 0) {
+      }
+      if (!CL && fuse_db && t.m_blk == 0 && q == 0) {
         // every row of the ones-accumulators holds the column sums; TMEM lane 0 belongs to lane 0 of this warp
 #pragma unroll 1
         for (int c = 0; c < BN / 32; ++c) {
@@ -369,7 +432,59 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CL) {
+    // ---- split-K reduction across the cluster through distributed shared memory, then the epilogue ----
+    cluster_sync_all();  // every CTA's partial tile is in its shared memory
+    constexpr int PITCH = BN + CL_PITCH_PAD;
+    const int S = p.splits;
+    const TileCoord t = decode_tile(tile_first, p);
+    const uint32_t part_addr = tiles;  // same offset in every CTA of the cluster
+    const int rows_per_cta = BLOCK_M / S;  // S divides 128
+    const int q4 = BN / 4;
+    for (int idx = threadIdx.x; idx < rows_per_cta * q4; idx += NUM_THREADS) {
+      const int r = (int)cl_rank * rows_per_cta + idx / q4, c4 = idx % q4;
+      const int row = t.m_blk * BLOCK_M + r, col = t.n_blk * BN + c4 * 4;
+      if (row >= p.M || col >= p.N) continue;  // N % 4 == 0: a group of 4 columns is all in or all out
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int src = 0; src < S; src += 4) {  // 4 remote loads in flight, summed in a fixed order (deterministic)
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          v[u] = (src + u < S) ? ld_dsmem4(part_addr + (uint32_t)(r * PITCH + c4 * 4) * 4u, (uint32_t)(src + u))
+                               : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+      }
+      float* dst = p.cl_w + (int64_t)row * p.N + col;
+      if (p.cl_apply) {
+        float4 w = *reinterpret_cast<const float4*>(dst);
+        w.x -= p.cl_lr * s.x; w.y -= p.cl_lr * s.y; w.z -= p.cl_lr * s.z; w.w -= p.cl_lr * s.w;
+        s = w;
+      }
+      *reinterpret_cast<float4*>(dst) = s;
+    }
+    if (t.m_blk == 0 && cl_rank == 0) {  // bias gradient of this column block
+      for (int c4 = threadIdx.x; c4 < q4; c4 += NUM_THREADS) {
+        const int col = t.n_blk * BN + c4 * 4;
+        if (col >= p.N) continue;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int src = 0; src < S; ++src) {
+          const float4 v = ld_dsmem4(part_addr + (uint32_t)(BLOCK_M * PITCH + c4 * 4) * 4u, (uint32_t)src);
+          s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+        }
+        float* dst = p.cl_b + col;
+        if (p.cl_apply) {
+          float4 b = *reinterpret_cast<const float4*>(dst);
+          b.x -= p.cl_lr * s.x; b.y -= p.cl_lr * s.y; b.z -= p.cl_lr * s.z; b.w -= p.cl_lr * s.w;
+          s = b;
+        }
+        *reinterpret_cast<float4*>(dst) = s;
+      }
+    }
+    cluster_sync_all();  // nobody leaves while a neighbour still reads its shared memory
+  } else {
+    __syncthreads();
+  }
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
@@ -433,7 +548,125 @@ int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Pa
   return launch_one<A_MN, B_MN, 32, Epi>(ta, tb, p, epi, st);
 }
 
+// Cluster split-K plan of the dW GEMM: S CTAs per output tile, S in {16, 8, 4, 2} (S divides the 128 tile rows).
+// Wanted: one wave (tiles * S <= SMs), >= 2 k-blocks per split, accumulation chains within DDNN_TF32_MAX_CHAIN
+// (S >= B / 2048), 16-byte aligned outputs.  Returns 0 when no S fits (the workspace path takes the layer).
+template <int BN>
+int cluster_splits_for(int64_t B, int64_t K, int64_t N, int* max_clusters_out) {
+  const long tiles = (long)cdiv(K, BLOCK_M) * cdiv(N, BN);
+  const long num_kb = cdiv(B, BLOCK_K);
+  const long min_by_chain = cdiv(B, DDNN_TF32_MAX_CHAIN);
+  auto kern = tf32_gemm_kernel<true, true, BN, EpiStoreF32, true>;
+  if (ensure_dynamic_smem((const void*)kern, TCfg<BN>::SMEM_BYTES) != DDNN_OK) return 0;
+  for (int S : {16, 8, 4, 2}) {
+    if (tiles * S > ctas_available() || num_kb / S < 2 || S < min_by_chain) continue;
+    if (S > 8 && cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(tiles * S));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = TCfg<BN>::SMEM_BYTES;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int max_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&max_clusters, (const void*)kern, &cfg) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    if (max_clusters >= tiles) {  // all clusters co-resident: one wave
+      if (max_clusters_out) *max_clusters_out = max_clusters;
+      return S;
+    }
+  }
+  return 0;
+}
+
+template <int BN>
+int launch_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Params& p, cudaStream_t st) {
+  auto kern = tf32_gemm_kernel<true, true, BN, EpiStoreF32, true>;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)(p.m_blocks * p.n_blocks * p.splits));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = TCfg<BN>::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = p.splits;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 2 : 1;
+  EpiStoreF32 unused{nullptr, 0};
+  DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, unused));
+  count_launch();
+  return DDNN_OK;
+}
+
+std::atomic<int> g_cluster_dw{1};
+
 }  // namespace
+
+void tf32_set_cluster_dw(int on) { g_cluster_dw.store(on ? 1 : 0); }
+
+static int dw_bn(int64_t N);
+
+// dW + db with the split-K reduction inside the kernel (thread-block cluster, distributed shared memory): writes the
+// final result -- SGD on W_master / bias (apply) or the fp32 gradients -- in ONE launch, no workspace traffic.
+// *taken = 0 when the shape has no cluster plan (the caller then runs the workspace path).
+int tf32_dw_cluster(const float* X, const float* dZ, float* W_master, float* bias, float* dW_out, float* db_out, float lr,
+                    int apply, int64_t B, int64_t K, int64_t N, int* taken, cudaStream_t st) {
+  *taken = 0;
+  if (!g_cluster_dw.load()) return DDNN_OK;
+  float* w = apply ? W_master : dW_out;
+  float* b = apply ? bias : db_out;
+  if ((reinterpret_cast<uintptr_t>(w) & 15u) || (reinterpret_cast<uintptr_t>(b) & 15u)) return DDNN_OK;
+  const int bn = dw_bn(N);
+  static_assert(BLOCK_M * (128 + CL_PITCH_PAD) * 4 + 128 * 4 <= TCfg<128>::STAGES * (int)TCfg<128>::STAGE_BYTES &&
+                BLOCK_M * (64 + CL_PITCH_PAD) * 4 + 64 * 4 <= TCfg<64>::STAGES * (int)TCfg<64>::STAGE_BYTES &&
+                BLOCK_M * (32 + CL_PITCH_PAD) * 4 + 32 * 4 <= TCfg<32>::STAGES * (int)TCfg<32>::STAGE_BYTES,
+                "the partial tile must fit in the operand ring it overlays");
+  // the plan needs an occupancy query: look it up once per (device, shape)
+  static std::mutex mu;
+  static std::map<std::tuple<int, int64_t, int64_t, int64_t>, int> plans;
+  int dev = 0, S = -1;
+  DDNN_CUDA_CHECK(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = plans.find(std::make_tuple(dev, B, K, N));
+    if (it != plans.end()) S = it->second;
+  }
+  if (S < 0) {
+    S = bn == 128 ? cluster_splits_for<128>(B, K, N, nullptr)
+                  : (bn == 64 ? cluster_splits_for<64>(B, K, N, nullptr) : cluster_splits_for<32>(B, K, N, nullptr));
+    std::lock_guard<std::mutex> g(mu);
+    if (plans.size() > 4096) plans.clear();
+    plans[std::make_tuple(dev, B, K, N)] = S;
+  }
+  if (S == 0) return DDNN_OK;
+  CUtensorMap ta, tb;
+  int rc = operand_maps(true, X, true, dZ, K, N, B, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  Tf32Params p{};
+  fill_tiles(p, K, N, B, bn, S);
+  if (p.splits != S) return DDNN_OK;  // the k-blocks do not split S ways: leave it to the workspace path
+  p.cl_w = w;
+  p.cl_b = b;
+  p.cl_lr = lr;
+  p.cl_apply = apply ? 1 : 0;
+  *taken = 1;
+  if (bn == 128) return launch_cluster<128>(ta, tb, p, st);
+  if (bn == 64) return launch_cluster<64>(ta, tb, p, st);
+  return launch_cluster<32>(ta, tb, p, st);
+}
 
 // TMA needs 16-byte row pitches (widths % 4) and the boxes are 32 elements wide
 bool tf32_shape_ok(int64_t B, int64_t K, int64_t N) {

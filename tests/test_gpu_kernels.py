@@ -390,3 +390,32 @@ def _tail2_case(ops, case):
     # shapes the kernel does not take: no workspace, DDNN_ERR_UNSUPPORTED
     assert ops.tail2_workspace_bytes(b, 256, 64, 10, torch.float32) == 0
     assert ops.tail2_workspace_bytes(b, 128, 64, 10, torch.bfloat16) == 0
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("shape", [(4096, 784, 128), (1000, 300, 72), (512, 128, 64), (3000, 256, 256), (96, 64, 48)])
+def test_cluster_split_k_dw_f32(cuda_device, shape):
+    """fp32 dW with the split-K reduction inside the kernel (thread-block cluster + distributed shared memory, SGD
+    applied by the same kernel): gradients and fused update against the float64 oracle and against the workspace +
+    reducer path (same products, different summation order of the partial tiles), run-to-run bit-identical."""
+    from ddnn_b200 import _lib, ops
+    b, k, n = shape
+    rng = np.random.default_rng(40)
+    x, dz = rng.random((b, k)), rng.standard_normal((b, n)) / b
+    w, bias = rng.standard_normal((k, n)), rng.standard_normal(n)
+    xd, dzd = to_dev(x), to_dev(dz)
+    dw, db = ops.dense_backward_dw(xd, dzd)
+    dw2, db2 = ops.dense_backward_dw(xd, dzd)
+    assert torch.equal(dw, dw2) and torch.equal(db, db2)
+    assert rel_err(to_np(dw), np.dot(x.T, dz)) < F32_TOL and rel_err(to_np(db), dz.sum(axis=0)) < F32_TOL
+    assert cond_ok(to_np(dw), np.dot(x.T, dz), np.dot(np.abs(x).T, np.abs(dz)), F32_TOL)
+    wd, bd = to_dev(w), to_dev(bias)
+    ops.dense_backward_dw_sgd(xd, dzd, wd, bd, 0.1)
+    assert rel_err(to_np(wd), w - 0.1 * np.dot(x.T, dz)) < F32_TOL
+    assert rel_err(to_np(bd), bias - 0.1 * dz.sum(axis=0)) < F32_TOL
+    _lib.check(_lib.lib.ddnn_set_cluster_split_k(0))
+    try:
+        dw_ws, db_ws = ops.dense_backward_dw(xd, dzd)
+    finally:
+        _lib.check(_lib.lib.ddnn_set_cluster_split_k(1))
+    assert rel_err(to_np(dw), to_np(dw_ws)) < 2e-6 and rel_err(to_np(db), to_np(db_ws)) < 2e-6
