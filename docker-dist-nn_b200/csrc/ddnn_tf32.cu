@@ -19,6 +19,7 @@
 // Same three operand layouts as the bf16 family (descriptor major-ness instead of transposes in memory).
 #include <cuda.h>
 
+#include <cstdlib>
 #include <map>
 #include <mutex>
 #include <tuple>
@@ -558,7 +559,9 @@ int cluster_splits_for(int64_t B, int64_t K, int64_t N, int* max_clusters_out) {
   const long min_by_chain = cdiv(B, DDNN_TF32_MAX_CHAIN);
   auto kern = tf32_gemm_kernel<true, true, BN, EpiStoreF32, true>;
   if (ensure_dynamic_smem((const void*)kern, TCfg<BN>::SMEM_BYTES) != DDNN_OK) return 0;
+  static const int dbg_max_s = getenv("DDNN_DBG_CLUSTER_S") ? atoi(getenv("DDNN_DBG_CLUSTER_S")) : 16;  // measurement knob
   for (int S : {16, 8, 4, 2}) {
+    if (S > dbg_max_s) continue;
     if (tiles * S > ctas_available() || num_kb / S < 2 || S < min_by_chain) continue;
     if (S > 8 && cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
       cudaGetLastError();
@@ -706,7 +709,11 @@ int tf32_dx(const float* dZ, const float* W, const float* Aprev, float* dZprev, 
   return launch_bn<false, false, EpiDx<float>>(bn, ta, tb, p, epi, st);
 }
 
-static int dw_bn(int64_t N) { return N >= 128 ? 128 : (N >= 64 ? 64 : 32); }
+static int dw_bn(int64_t N) {
+  static const int dbg = getenv("DDNN_DBG_DW_BN") ? atoi(getenv("DDNN_DBG_DW_BN")) : 0;  // measurement knob
+  if (dbg == 128 || dbg == 64 || dbg == 32) return N >= dbg ? dbg : 32;
+  return N >= 128 ? 128 : (N >= 64 ? 64 : 32);
+}
 
 int tf32_dw_splits(int64_t B, int64_t K, int64_t N) {
   const int bn = dw_bn(N);

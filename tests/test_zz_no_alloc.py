@@ -115,13 +115,15 @@ def test_no_device_memory_is_taken_by_the_call(cuda_device):
     _static_call(xd, dzd, dw=dw, db=db)      # one-time set-up on this device happens here at the latest
     torch.cuda.synchronize()
     free0, _ = torch.cuda.mem_get_info()
-    alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    st0 = torch.cuda.memory_stats()
     for _ in range(5):
         _static_call(xd, dzd, dw=dw, db=db)
     torch.cuda.synchronize()
     free1, _ = torch.cuda.mem_get_info()
-    assert free1 == free0
-    assert torch.cuda.memory_allocated() == alloc0 and torch.cuda.memory_reserved() == reserved0
+    st1 = torch.cuda.memory_stats()
+    assert free1 == free0                                                     # the driver handed out nothing
+    for counter in ("allocation.all.allocated", "segment.all.allocated"):     # and torch was asked for nothing
+        assert st1[counter] == st0[counter], counter
 
 
 @pytest.mark.skipif(not torch.cuda.is_available() or torch.cuda.device_count() < 2, reason="needs a second GPU")

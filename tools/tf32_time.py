@@ -8,6 +8,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from ddnn_b200 import _lib, ops  # noqa: E402
 
 _lib.set_f32_tensor_cores(int(os.environ.get("MODE", "2")))
+_lib.check(_lib.lib.ddnn_set_cluster_split_k(int(os.environ.get("CLUSTER", "1"))))
 dev = torch.device("cuda", 0)
 shapes = [tuple(int(v) for v in a.split("x")) for a in sys.argv[1:]] or [(4096, 784, 128), (4096, 128, 64), (16384, 784, 128), (4096, 2048, 512)]
 for (b, k, n) in shapes:
