@@ -22,6 +22,20 @@ from ddnn_b200 import Layer  # noqa: E402
 from ddnn_b200.pipeline import PipelineStage, stage_assignment  # noqa: E402
 
 
+def nvlink_kib(index: int):
+    """(tx, rx) KiB summed over this GPU's NVLink links, from `nvidia-smi nvlink -gt d`; None when unavailable."""
+    import re
+    import subprocess
+    try:
+        out = subprocess.run(["nvidia-smi", "nvlink", "-gt", "d", "-i", str(index)], stdout=subprocess.PIPE,
+                             stderr=subprocess.STDOUT, text=True, timeout=20).stdout
+    except Exception:  # noqa: BLE001
+        return None
+    tx = sum(int(v) for v in re.findall(r"Data Tx:\s*(\d+)\s*KiB", out))
+    rx = sum(int(v) for v in re.findall(r"Data Rx:\s*(\d+)\s*KiB", out))
+    return (tx, rx) if (tx or rx) else None
+
+
 def main():
     workload = sys.argv[1] if len(sys.argv) > 1 else "wide8x16384"
     out = sys.argv[2] if len(sys.argv) > 2 else os.path.join(REPO, "gpurun_out", "timeline")
@@ -59,13 +73,18 @@ def main():
     for _ in range(2):
         stage.train_step(x, y, rows, micro, LR)
     barrier()
+    nv0 = nvlink_kib(local)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(3):
         stage.train_step(x, y, rows, micro, LR)
     e1.record()
     barrier()
+    nv1 = nvlink_kib(local)
     plain_ms = e0.elapsed_time(e1) / 3
+    nv = ""
+    if nv0 and nv1:  # what the fused epilogue stores put on the wire per step (activations out / gradients in, ...)
+        nv = f" | NVLink per step: tx {(nv1[0] - nv0[0]) / 3 / 2**20:.3f} GiB, rx {(nv1[1] - nv0[1]) / 3 / 2**20:.3f} GiB"
     layer._probe = []
     barrier()
     start = torch.cuda.Event(enable_timing=True)
@@ -99,7 +118,7 @@ def main():
             f"(idle inside {bidle:.2f}) | update {u0:.2f}-{u1:.2f} (idle inside {uidle:.2f}) | mean GEMM: fwd "
             f"{sum(d for _, _, d in fwd) / max(1, len(fwd)):.4f} ms, dX "
             f"{sum(r[2] for r in bwd if r[0].startswith('dX')) / max(1, len([r for r in bwd if r[0].startswith('dX')])):.4f} ms, "
-            f"dW {sum(d for _, _, d in upd) / max(1, len(upd)):.3f} ms")
+            f"dW {sum(d for _, _, d in upd) / max(1, len(upd)):.3f} ms{nv}")
     if world > 1:
         lines = [None] * world
         dist.all_gather_object(lines, line)
