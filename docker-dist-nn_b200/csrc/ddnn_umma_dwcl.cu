@@ -1,0 +1,368 @@
+// bf16 weight gradient with the split-K reduction INSIDE the kernel:  dW[K,N] = X[B,K]^T . dZ[B,N],
+// db[N] = column sums of dZ, then SGD (W_master / bf16 shadow / bias) or fp32 gradient store -- one launch.
+//
+// The split-K plan of ddnn_umma.cu writes one fp32 partial tile per (tile, split) to a workspace and a second
+// kernel re-reads and reduces them: for the narrow layers (784 x 256 at batch 65536: 7 tiles x 21 splits) that is
+// 19 MB of partials and a 12-17 us reducer launch on the critical path of a 170 us step.  Here the S CTAs that
+// share an output tile form a thread-block cluster: each reduces its share of the batch into TMEM
+// (tcgen05.mma.kind::f16, both operands MN-major, TMA-fed, like umma_gemm_kernel<true, true>), parks the partial
+// tile in shared memory over the operand ring, and after a cluster barrier every CTA sums 128 / S rows of the tile
+// over the S partials through distributed shared memory and applies the epilogue itself.  The bias gradient gets
+// clusters of its own (one per column block): their CTAs load only the dZ tiles and multiply them by an all-ones
+// operand, so no tile's cluster carries extra MMAs (in the workspace kernel the CTAs of row-block 0 did, and the
+// whole grid waited 22 % longer for them).
+#include <cuda.h>
+
+#include <cstdlib>
+#include <map>
+#include <mutex>
+#include <tuple>
+
+#include "ddnn_umma.cuh"
+
+namespace ddnn {
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int BLOCK_K = 64;
+constexpr int UMMA_K = 16;
+constexpr int NUM_THREADS = 256;
+constexpr int PITCH_PAD = 4;  // floats of padding per partial-tile row
+
+struct DwClParams {
+  int M, N;                 // output rows (= layer inputs K) and columns
+  int m_blocks, n_blocks;   // real tiles; clusters [m_blocks * n_blocks, (m_blocks + 1) * n_blocks) are the bias clusters
+  int num_kb, kb_per_split, splits;
+  float* w;                 // apply: W_master (updated in place); else dW_out
+  bf16* shadow;             // apply: bf16 copy of W_master (nullable)
+  float* b;                 // apply: bias; else db_out
+  float lr;
+  int apply;
+};
+
+template <int BN>
+struct ClCfg {
+  static constexpr int STAGES = BN == 256 ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
+  static constexpr uint32_t B_BYTES = BN * BLOCK_K * 2;
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr uint32_t TMEM_COLS = BN;
+  static constexpr uint32_t BAR_BYTES = (2 * STAGES + 1) * 8 + 16;
+  static constexpr uint32_t ONES_BYTES = 2048;
+  static constexpr uint32_t PART_BYTES = BLOCK_M * (BN + PITCH_PAD) * 4;
+  static_assert(PART_BYTES <= STAGES * STAGE_BYTES, "the partial tile overlays the operand ring");
+  static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + 128 + ONES_BYTES;
+};
+
+__device__ __forceinline__ float4 ld_dsmem4(uint32_t local_addr, uint32_t cta) {
+  uint32_t ra;
+  float4 v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(local_addr), "r"(cta));
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"(ra)
+               : "memory");
+  return v;
+}
+
+// sum of the S partial values at `local_addr` of every CTA of the cluster, in CTA order (deterministic), 4 loads in flight
+__device__ __forceinline__ float4 cluster_sum4(uint32_t local_addr, int S) {
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int src = 0; src < S; src += 4) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      v[u] = (src + u < S) ? ld_dsmem4(local_addr, (uint32_t)(src + u)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
+  }
+  return s;
+}
+
+template <int BN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                       const DwClParams p) {
+  using C = ClCfg<BN>;
+  constexpr int PITCH = BN + PITCH_PAD;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t tiles = (raw + 1023u) & ~1023u;
+  const uint32_t bars = tiles + C::STAGES * C::STAGE_BYTES;
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (C::STAGES + s); };
+  const uint32_t tfull_bar = bars + 8u * (2 * C::STAGES);
+  const uint32_t tmem_slot = bars + 8u * (2 * C::STAGES + 1);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - raw));
+  const uint32_t ones_base = (bars + C::BAR_BYTES + 127u) & ~127u;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int S = p.splits;
+  const uint32_t rank = cluster_ctarank();          // = split index
+  const int cid = (int)(blockIdx.x / S);             // cluster = one tile (or one bias column block)
+  const int n_blk = cid % p.n_blocks, m_blk = cid / p.n_blocks;
+  const bool is_db = m_blk == p.m_blocks;            // bias cluster: ones . dZ
+  const int kb0 = (int)rank * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
+  pdl_launch_dependents();
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  if (is_db && warp == 3) {  // all-ones A operand: layout-invariant, 2 KB stand for the whole 128 x 64 tile (LBO = 0)
+    uint32_t* o = reinterpret_cast<uint32_t*>(smem_raw + (ones_base - raw));
+    for (int i = lane; i < (int)(C::ONES_BYTES / 4); i += 32) o[i] = 0x3F803F80u;
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_wait();
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t stage = 0, phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(empty_bar(stage), phase ^ 1);
+        mbar_expect_tx(full_bar(stage), is_db ? C::B_BYTES : C::STAGE_BYTES);
+        const uint32_t a_dst = tiles + stage * C::STAGE_BYTES;
+        const uint32_t b_dst = a_dst + C::A_BYTES;
+        if (!is_db) {
+#pragma unroll
+          for (int i = 0; i < BLOCK_M / 64; ++i)
+            tma_load_2d(a_dst + i * (BLOCK_K * 128), &tma_a, full_bar(stage), m_blk * BLOCK_M + i * 64, kb * BLOCK_K);
+        }
+#pragma unroll
+        for (int i = 0; i < BN / 64; ++i)
+          tma_load_2d(b_dst + i * (BLOCK_K * 128), &tma_b, full_bar(stage), n_blk * BN + i * 64, kb * BLOCK_K);
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      // kind::f16: D = f32, A = B = bf16, both MN-major, N = BN, M = 128
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+                                 ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
+      uint32_t stage = 0, phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+        const uint32_t a_base = tiles + stage * C::STAGE_BYTES;
+        const uint32_t b_base = a_base + C::A_BYTES;
+#pragma unroll
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+          const uint64_t adesc = is_db ? make_desc(ones_base, 0, 1024)
+                                       : make_desc(a_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024);
+          umma_bf16(tmem_base, adesc, make_desc(b_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024), idesc,
+                    (kb > kb0 || k > 0) ? 1u : 0u);
+        }
+        umma_commit(empty_bar(stage));
+        if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+      }
+      umma_commit(tfull_bar);
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue: accumulator -> shared memory (over the operand ring) =====================
+    const int q = warp & 3;
+    mbar_wait(tfull_bar, 0);  // every MMA has retired: nothing reads the ring any more, nothing is in flight into it
+    tc_fence_after();
+    float* part = reinterpret_cast<float*>(smem_raw + (tiles - raw));
+    if (!is_db) {
+      const int row = q * 32 + lane;
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        tmem_ld32(tmem_base + c * 32 + ((uint32_t)(q * 32) << 16), v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<float4*>(&part[row * PITCH + c * 32 + 4 * j]) =
+              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
+    } else if (q == 0) {  // every row of the ones-accumulator holds the column sums: TMEM lane 0 = lane 0 of this warp
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        float v[32];
+        tmem_ld32(tmem_base + c * 32, v);
+        tmem_ld_wait();
+        if (lane == 0) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) part[c * 32 + j] = v[j];
+        }
+      }
+    }
+  }
+
+  // ===================== split-K reduction across the cluster, then the epilogue =====================
+  tc_fence_before();
+  cluster_sync_all();  // every CTA's partial is in its shared memory
+  const uint32_t part_addr = tiles;  // same offset in every CTA of the cluster
+  constexpr int q4 = BN / 4;
+  if (!is_db) {
+    const int rows_per_cta = BLOCK_M / S;  // S divides 128
+    for (int idx = threadIdx.x; idx < rows_per_cta * q4; idx += NUM_THREADS) {
+      const int r = (int)rank * rows_per_cta + idx / q4, c4 = idx % q4;
+      const int row = m_blk * BLOCK_M + r, col = n_blk * BN + c4 * 4;
+      if (row >= p.M || col >= p.N) continue;  // N % 8 == 0: a group of 4 columns is all in or all out
+      float4 s = cluster_sum4(part_addr + (uint32_t)(r * PITCH + c4 * 4) * 4u, S);
+      float* dst = p.w + (int64_t)row * p.N + col;
+      if (p.apply) {
+        const float4 w = *reinterpret_cast<const float4*>(dst);
+        s = make_float4(w.x - p.lr * s.x, w.y - p.lr * s.y, w.z - p.lr * s.z, w.w - p.lr * s.w);
+        if (p.shadow) st4(p.shadow + (int64_t)row * p.N + col, s);
+      }
+      *reinterpret_cast<float4*>(dst) = s;
+    }
+  } else if (rank == 0) {
+    for (int c4 = threadIdx.x; c4 < q4; c4 += NUM_THREADS) {
+      const int col = n_blk * BN + c4 * 4;
+      if (col >= p.N) continue;
+      float4 s = cluster_sum4(part_addr + (uint32_t)(c4 * 4) * 4u, S);
+      float* dst = p.b + col;
+      if (p.apply) {
+        const float4 b = *reinterpret_cast<const float4*>(dst);
+        s = make_float4(b.x - p.lr * s.x, b.y - p.lr * s.y, b.z - p.lr * s.z, b.w - p.lr * s.w);
+      }
+      *reinterpret_cast<float4*>(dst) = s;
+    }
+  }
+  cluster_sync_all();  // nobody leaves while a neighbour still reads its shared memory
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+std::atomic<int> g_cluster_dw_bf16{1};
+
+template <int BN>
+int plan_splits(int64_t B, int64_t K, int64_t N) {
+  const long clusters = ((long)cdiv(K, BLOCK_M) + 1) * cdiv(N, BN);  // tiles + one bias cluster per column block
+  const long num_kb = cdiv(B, BLOCK_K);
+  const int sms = umma_num_sms() - umma_sm_reserve();
+  auto kern = umma_dw_cluster_kernel<BN>;
+  if (ensure_dynamic_smem((const void*)kern, ClCfg<BN>::SMEM_BYTES) != DDNN_OK) return 0;
+  for (int S : {16, 8, 4, 2}) {
+    // one wave, most of the machine in use (else the workspace plan with its finer splits wins), >= 4 k-blocks each
+    if (clusters * S > sms || clusters * S < (sms * 3) / 5 || num_kb / S < 4) continue;
+    if (S > 8 && cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)(clusters * S));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = ClCfg<BN>::SMEM_BYTES;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int max_clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&max_clusters, (const void*)kern, &cfg) != cudaSuccess) {
+      cudaGetLastError();
+      continue;
+    }
+    if (max_clusters >= clusters) return S;  // all clusters co-resident
+  }
+  return 0;
+}
+
+template <int BN>
+int launch(const CUtensorMap& ta, const CUtensorMap& tb, const DwClParams& p, cudaStream_t st) {
+  auto kern = umma_dw_cluster_kernel<BN>;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)((p.m_blocks + 1) * p.n_blocks * p.splits));
+  cfg.blockDim = dim3(NUM_THREADS);
+  cfg.dynamicSmemBytes = ClCfg<BN>::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = p.splits;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 2 : 1;
+  DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+  count_launch();
+  return DDNN_OK;
+}
+
+}  // namespace
+
+void umma_set_cluster_dw(int on) { g_cluster_dw_bf16.store(on ? 1 : 0); }
+
+// *taken = 0: no cluster plan for this shape (or switched off): the caller runs the workspace path.
+int umma_dw_cluster(const bf16* X, const bf16* dZ, float* W_master, bf16* W_shadow, float* bias, float* dW_out,
+                    float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N, int* taken, cudaStream_t st) {
+  *taken = 0;
+  if (!g_cluster_dw_bf16.load()) return DDNN_OK;
+  float* w = apply ? W_master : dW_out;
+  float* b = apply ? bias : db_out;
+  if (!w || !b || (reinterpret_cast<uintptr_t>(w) & 15u) || (reinterpret_cast<uintptr_t>(b) & 15u) ||
+      (apply && W_shadow && (reinterpret_cast<uintptr_t>(W_shadow) & 7u)))
+    return DDNN_OK;
+  const int bn = N >= 192 ? 256 : (N >= 96 ? 128 : 64);
+  static std::mutex mu;
+  static std::map<std::tuple<int, int64_t, int64_t, int64_t>, int> plans;  // occupancy query once per (device, shape)
+  int dev = 0, S = -1;
+  DDNN_CUDA_CHECK(cudaGetDevice(&dev));
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = plans.find(std::make_tuple(dev, B, K, N));
+    if (it != plans.end()) S = it->second;
+  }
+  if (S < 0) {
+    S = bn == 256 ? plan_splits<256>(B, K, N) : (bn == 128 ? plan_splits<128>(B, K, N) : plan_splits<64>(B, K, N));
+    std::lock_guard<std::mutex> g(mu);
+    if (plans.size() > 4096) plans.clear();
+    plans[std::make_tuple(dev, B, K, N)] = S;
+  }
+  if (S == 0) return DDNN_OK;
+  DwClParams p{};
+  p.M = (int)K;
+  p.N = (int)N;
+  p.m_blocks = cdiv(K, BLOCK_M);
+  p.n_blocks = cdiv(N, bn);
+  p.num_kb = cdiv(B, BLOCK_K);
+  p.kb_per_split = cdiv(p.num_kb, S);
+  if (cdiv(p.num_kb, p.kb_per_split) != S) return DDNN_OK;  // the k-blocks do not split S ways
+  p.splits = S;
+  p.w = w;
+  p.shadow = apply ? W_shadow : nullptr;
+  p.b = b;
+  p.lr = lr;
+  p.apply = apply ? 1 : 0;
+  CUtensorMap ta, tb;
+  int rc = umma_get_tmap(X, 2, (uint64_t)K, (uint64_t)B, 64, 64, 0, &ta);  // MN-major: stored [B][K], box {64 K, 64 rows}
+  if (rc != DDNN_OK) return rc;
+  rc = umma_get_tmap(dZ, 2, (uint64_t)N, (uint64_t)B, 64, 64, 0, &tb);
+  if (rc != DDNN_OK) return rc;
+  *taken = 1;
+  if (bn == 256) return launch<256>(ta, tb, p, st);
+  if (bn == 128) return launch<128>(ta, tb, p, st);
+  return launch<64>(ta, tb, p, st);
+}
+
+}  // namespace ddnn
