@@ -359,7 +359,8 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None):
            "pool_batches": pool_n, "pool_bytes": pool_n * batch_bytes, "cuda_graph": use_graph}
     # ---- e2e: HOST buffers, H2D of the batch + D2H of the loss inside the timed region, through
     # the public call Trainer.train_step_host ----
-    hx = [torch.rand((rows, dims[0]), dtype=torch.float32).pin_memory() for _ in range(4)]
+    # host rows in the compute dtype (like the wide nets' e2e): a bf16 model is fed bf16 rows
+    hx = [torch.rand((rows, dims[0]), dtype=torch.float32).to(xdt).pin_memory() for _ in range(4)]
     hy = [torch.randint(0, dims[-1], (rows,), dtype=torch.int32).pin_memory() for _ in range(4)]
     # the host loop is PCIe-bound at ~1 ms per step or less: time enough steps for a stable figure
     e2e_steps = max(200 if use_graph else 3, min(steps, 400))
@@ -371,13 +372,13 @@ def bench_single(workload, dtype, steps, warmup, device, barrier=None):
             losses = tr.fit_stream([(hx[i & 3], hy[i & 3]) for i in range(e2e_steps)])
             assert len(losses) == e2e_steps and all(np.isfinite(losses))
         ms_e2e = timed(e2e_run, 1, 1, device, barrier)
-        api = "Trainer.fit_stream (pinned host batches -> H2D on a copy stream overlapped with the step -> loss D2H)"
+        api = "Trainer.fit_stream (pinned host batches in the compute dtype -> H2D on a copy stream overlapped with the step -> loss D2H)"
     else:
         def e2e_step(i):
             tr.train_step_host(hx[i & 3], hy[i & 3])
         ms_e2e = timed(e2e_step, e2e_steps, min(warmup, 5), device, barrier)
         api = "Trainer.train_step_host (pinned host batch -> H2D -> step -> loss D2H)"
-    res.update({"e2e_ms_total": ms_e2e, "e2e_steps": e2e_steps, "h2d": rows * dims[0] * 4 + rows * 4, "d2h": 4,
+    res.update({"e2e_ms_total": ms_e2e, "e2e_steps": e2e_steps, "h2d": rows * dims[0] * elt + rows * 4, "d2h": 4,
                 "e2e_api": api})
     return res, tr, xs, ys
 

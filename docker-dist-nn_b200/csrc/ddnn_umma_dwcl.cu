@@ -216,11 +216,11 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const uint32_t part_addr = tiles;  // same offset in every CTA of the cluster
   constexpr int q4 = BN / 4;
   if (!is_db) {
-    const int rows_per_cta = BLOCK_M / S;  // S divides 128
+    const int rows_per_cta = (BLOCK_M + S - 1) / S;  // any cluster size: the last CTAs take the remainder
     for (int idx = threadIdx.x; idx < rows_per_cta * q4; idx += NUM_THREADS) {
       const int r = (int)rank * rows_per_cta + idx / q4, c4 = idx % q4;
       const int row = m_blk * BLOCK_M + r, col = n_blk * BN + c4 * 4;
-      if (row >= p.M || col >= p.N) continue;  // N % 8 == 0: a group of 4 columns is all in or all out
+      if (r >= BLOCK_M || row >= p.M || col >= p.N) continue;  // N % 8 == 0: 4 columns are all in or all out
       float4 s = cluster_sum4(part_addr + (uint32_t)(r * PITCH + c4 * 4) * 4u, S);
       float* dst = p.w + (int64_t)row * p.N + col;
       if (p.apply) {
@@ -259,9 +259,11 @@ int plan_splits(int64_t B, int64_t K, int64_t N) {
   const int sms = umma_num_sms() - umma_sm_reserve();
   auto kern = umma_dw_cluster_kernel<BN>;
   if (ensure_dynamic_smem((const void*)kern, ClCfg<BN>::SMEM_BYTES) != DDNN_OK) return 0;
-  for (int S : {16, 8, 4, 2}) {
+  static const int dbg = getenv("DDNN_DBG_CLUSTER_PRINT") ? 1 : 0;
+  for (int S = 16; S >= 2; --S) {  // the largest cluster whose clusters are all co-resident (GPCs differ in size)
     // one wave, most of the machine in use (else the workspace plan with its finer splits wins), >= 4 k-blocks each
     if (clusters * S > sms || clusters * S < (sms * 3) / 5 || num_kb / S < 4) continue;
+    if (cdiv(num_kb, cdiv(num_kb, S)) != S) continue;  // the k-blocks do not split S ways
     if (S > 8 && cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
       cudaGetLastError();
       continue;
@@ -282,6 +284,7 @@ int plan_splits(int64_t B, int64_t K, int64_t N) {
       cudaGetLastError();
       continue;
     }
+    if (dbg) fprintf(stderr, "ddnn dw cluster plan: BN=%d clusters=%ld S=%d max_active_clusters=%d\n", BN, clusters, S, max_clusters);
     if (max_clusters >= clusters) return S;  // all clusters co-resident
   }
   return 0;

@@ -143,15 +143,15 @@ class Trainer:
             loss = self.train_step(x, y, lr)
         return float(loss.item())
 
-    def _stream_setup(self, rows: int, lr: Optional[float]) -> None:
-        """Two device staging slots, one captured step per slot, a copy stream and the events
-        that order (H2D of slot s) -> (step on slot s) -> (next H2D into slot s)."""
+    def _stream_setup(self, rows: int, lr: Optional[float], x_dtype: torch.dtype = torch.float32) -> None:
+        """Two device staging slots (in the host batches' dtype), one captured step per slot, a copy stream and
+        the events that order (H2D of slot s) -> (step on slot s) -> (next H2D into slot s)."""
         dev = self.device
         self.layer.begin_batch(rows)
-        key = (rows, lr, self.layer._gen)  # a reallocation of the batch buffers invalidates the graphs
+        key = (rows, lr, self.layer._gen, x_dtype)  # a reallocation of the batch buffers invalidates the graphs
         if self._pinned is not None and self._pinned["key"] == key:
             return
-        sx = [torch.zeros((rows, self.in_dim), dtype=torch.float32, device=dev) for _ in range(2)]
+        sx = [torch.zeros((rows, self.in_dim), dtype=x_dtype, device=dev) for _ in range(2)]
         sy = [torch.zeros((rows,), dtype=torch.int32, device=dev) for _ in range(2)]
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -171,8 +171,9 @@ class Trainer:
                         "done": [torch.cuda.Event() for _ in range(2)]}
 
     def fit_stream(self, batches, lr: Optional[float] = None) -> List[float]:
-        """Trains on a sequence of HOST batches ``(x_pinned fp32 (B, in), y_pinned int32 (B,))``
-        in order.  The H2D copy of batch i+1 runs on a copy stream while batch i computes
+        """Trains on a sequence of HOST batches ``(x_pinned (B, in), y_pinned int32 (B,))`` in order; ``x`` is fp32
+        or already in the compute dtype (a bf16 model fed bf16 rows moves half the bytes over PCIe and the step
+        reads the staging slot in place; fp32 rows are cast on the device).  The H2D copy of batch i+1 runs on a copy stream while batch i computes
         (double-buffered staging slots, one captured CUDA graph per slot); each step's loss is
         copied back to pinned host memory asynchronously and all losses are returned after one
         final synchronisation.  Batches whose row count differs from the first (a ragged tail)
@@ -182,7 +183,7 @@ class Trainer:
             return []
         dev = self.device
         rows = batches[0][0].shape[0]
-        self._stream_setup(rows, lr)
+        self._stream_setup(rows, lr, batches[0][0].dtype)
         st = self._pinned
         losses_host = torch.empty((len(batches),), dtype=torch.float32).pin_memory()
         tail = {}
