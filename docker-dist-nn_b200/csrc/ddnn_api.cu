@@ -363,7 +363,7 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
     if (splits > 1) {  // split-K reduced inside the kernel across a thread-block cluster when a one-wave plan exists
       int taken = 0;
       rc = umma_dw_cluster((const bf16*)X, (const bf16*)dZ, W_master, (bf16*)W_shadow, bias, dW_out, db_out, lr, apply,
-                           B, K, N, &taken, st);
+                           B, K, N, ws, &taken, st);
       if (rc || taken) return rc;
     }
     float* dw_part = splits > 1 ? ws : nullptr;

@@ -7,10 +7,14 @@
 // share an output tile form a thread-block cluster: each reduces its share of the batch into TMEM
 // (tcgen05.mma.kind::f16, both operands MN-major, TMA-fed, like umma_gemm_kernel<true, true>), parks the partial
 // tile in shared memory over the operand ring, and after a cluster barrier every CTA sums 128 / S rows of the tile
-// over the S partials through distributed shared memory and applies the epilogue itself.  The bias gradient gets
-// clusters of its own (one per column block): their CTAs load only the dZ tiles and multiply them by an all-ones
-// operand, so no tile's cluster carries extra MMAs (in the workspace kernel the CTAs of row-block 0 did, and the
-// whole grid waited 22 % longer for them).
+// over the S partials through distributed shared memory and applies the epilogue itself.  The bias gradient
+// (ones . dZ on the tensor core, from the dZ tiles that are in shared memory anyway) is spread over the row-block
+// clusters: the cluster of row block m takes the k-blocks with kb % m_blocks == m, so every CTA carries 1 / m_blocks
+// of the extra MMAs (in the workspace kernel the CTAs of row-block 0 carried all of them and the whole grid waited
+// 22 % longer for them); each cluster reduces its share through shared memory, writes ONE bias partial to the
+// workspace, and a one-row reducer launch (m_blocks partials) applies it.  (A B200 shows 7 GPCs that can hold a
+// 16-CTA cluster and one that cannot -- cudaOccupancyMaxActiveClusters = 7 for every size above 8 -- so the plan needs
+// at most 7 tiles; a bias cluster of its own would be the eighth.)
 #include <cuda.h>
 
 #include <cstdlib>
@@ -31,11 +35,12 @@ constexpr int PITCH_PAD = 4;  // floats of padding per partial-tile row
 
 struct DwClParams {
   int M, N;                 // output rows (= layer inputs K) and columns
-  int m_blocks, n_blocks;   // real tiles; clusters [m_blocks * n_blocks, (m_blocks + 1) * n_blocks) are the bias clusters
+  int m_blocks, n_blocks;   // output tiles = clusters
+  float* db_part;           // [m_blocks][db_np] bias-gradient partials (one per row-block cluster), reduced by the caller
+  int db_np;
   int num_kb, kb_per_split, splits;
   float* w;                 // apply: W_master (updated in place); else dW_out
   bf16* shadow;             // apply: bf16 copy of W_master (nullable)
-  float* b;                 // apply: bias; else db_out
   float lr;
   int apply;
 };
@@ -46,10 +51,10 @@ struct ClCfg {
   static constexpr uint32_t A_BYTES = BLOCK_M * BLOCK_K * 2;
   static constexpr uint32_t B_BYTES = BN * BLOCK_K * 2;
   static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr uint32_t TMEM_COLS = BN;
+  static constexpr uint32_t TMEM_COLS = 2 * BN;  // tile accumulator | bias-gradient accumulator
   static constexpr uint32_t BAR_BYTES = (2 * STAGES + 1) * 8 + 16;
   static constexpr uint32_t ONES_BYTES = 2048;
-  static constexpr uint32_t PART_BYTES = BLOCK_M * (BN + PITCH_PAD) * 4;
+  static constexpr uint32_t PART_BYTES = (BLOCK_M + 1) * (BN + PITCH_PAD) * 4;  // + one row: the bias partial
   static_assert(PART_BYTES <= STAGES * STAGE_BYTES, "the partial tile overlays the operand ring");
   static constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + BAR_BYTES + 128 + ONES_BYTES;
 };
@@ -101,7 +106,6 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   const uint32_t rank = cluster_ctarank();          // = split index
   const int cid = (int)(blockIdx.x / S);             // cluster = one tile (or one bias column block)
   const int n_blk = cid % p.n_blocks, m_blk = cid / p.n_blocks;
-  const bool is_db = m_blk == p.m_blocks;            // bias cluster: ones . dZ
   const int kb0 = (int)rank * p.kb_per_split, kb1 = min(p.num_kb, kb0 + p.kb_per_split);
   pdl_launch_dependents();
 
@@ -121,7 +125,10 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
     tmem_alloc(tmem_slot, C::TMEM_COLS);
     tmem_relinquish();
   }
-  if (is_db && warp == 3) {  // all-ones A operand: layout-invariant, 2 KB stand for the whole 128 x 64 tile (LBO = 0)
+  // k-blocks of this CTA whose dZ tile also feeds the bias gradient: kb % m_blocks == m_blk
+  int n_ones = 0;
+  for (int kb = kb0; kb < kb1; ++kb) n_ones += (kb % p.m_blocks == m_blk) ? 1 : 0;
+  if (warp == 3) {  // all-ones A operand: layout-invariant, 2 KB stand for the whole 128 x 64 tile (LBO = 0)
     uint32_t* o = reinterpret_cast<uint32_t*>(smem_raw + (ones_base - raw));
     for (int i = lane; i < (int)(C::ONES_BYTES / 4); i += 32) o[i] = 0x3F803F80u;
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -138,14 +145,12 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       uint32_t stage = 0, phase = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(empty_bar(stage), phase ^ 1);
-        mbar_expect_tx(full_bar(stage), is_db ? C::B_BYTES : C::STAGE_BYTES);
+        mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
         const uint32_t a_dst = tiles + stage * C::STAGE_BYTES;
         const uint32_t b_dst = a_dst + C::A_BYTES;
-        if (!is_db) {
 #pragma unroll
-          for (int i = 0; i < BLOCK_M / 64; ++i)
-            tma_load_2d(a_dst + i * (BLOCK_K * 128), &tma_a, full_bar(stage), m_blk * BLOCK_M + i * 64, kb * BLOCK_K);
-        }
+        for (int i = 0; i < BLOCK_M / 64; ++i)
+          tma_load_2d(a_dst + i * (BLOCK_K * 128), &tma_a, full_bar(stage), m_blk * BLOCK_M + i * 64, kb * BLOCK_K);
 #pragma unroll
         for (int i = 0; i < BN / 64; ++i)
           tma_load_2d(b_dst + i * (BLOCK_K * 128), &tma_b, full_bar(stage), n_blk * BN + i * 64, kb * BLOCK_K);
@@ -160,17 +165,22 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                                  ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BLOCK_M >> 4) << 24);
       uint32_t stage = 0, phase = 0;
+      bool db_started = false;
       for (int kb = kb0; kb < kb1; ++kb) {
         mbar_wait(full_bar(stage), phase);
         tc_fence_after();
         const uint32_t a_base = tiles + stage * C::STAGE_BYTES;
         const uint32_t b_base = a_base + C::A_BYTES;
 #pragma unroll
-        for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-          const uint64_t adesc = is_db ? make_desc(ones_base, 0, 1024)
-                                       : make_desc(a_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024);
-          umma_bf16(tmem_base, adesc, make_desc(b_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024), idesc,
-                    (kb > kb0 || k > 0) ? 1u : 0u);
+        for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+          umma_bf16(tmem_base, make_desc(a_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024),
+                    make_desc(b_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024), idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+        if (kb % p.m_blocks == m_blk) {  // this cluster's share of the bias gradient: ones . dZ tile
+#pragma unroll
+          for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+            umma_bf16(tmem_base + BN, make_desc(ones_base, 0, 1024),
+                      make_desc(b_base + k * (UMMA_K * 128), BLOCK_K * 128, 1024), idesc, (db_started || k > 0) ? 1u : 0u);
+          db_started = true;
         }
         umma_commit(empty_bar(stage));
         if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
@@ -184,27 +194,26 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
     mbar_wait(tfull_bar, 0);  // every MMA has retired: nothing reads the ring any more, nothing is in flight into it
     tc_fence_after();
     float* part = reinterpret_cast<float*>(smem_raw + (tiles - raw));
-    if (!is_db) {
-      const int row = q * 32 + lane;
+    const int row = q * 32 + lane;
 #pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        float v[32];
-        tmem_ld32(tmem_base + c * 32 + ((uint32_t)(q * 32) << 16), v);
-        tmem_ld_wait();
+    for (int c = 0; c < BN / 32; ++c) {
+      float v[32];
+      tmem_ld32(tmem_base + c * 32 + ((uint32_t)(q * 32) << 16), v);
+      tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          *reinterpret_cast<float4*>(&part[row * PITCH + c * 32 + 4 * j]) =
-              make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-      }
-    } else if (q == 0) {  // every row of the ones-accumulator holds the column sums: TMEM lane 0 = lane 0 of this warp
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(&part[row * PITCH + c * 32 + 4 * j]) =
+            make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    if (q == 0) {  // every row of the ones-accumulator holds the column sums: TMEM lane 0 = lane 0 of this warp
 #pragma unroll 1
       for (int c = 0; c < BN / 32; ++c) {
         float v[32];
-        tmem_ld32(tmem_base + c * 32, v);
+        tmem_ld32(tmem_base + BN + c * 32, v);
         tmem_ld_wait();
         if (lane == 0) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) part[c * 32 + j] = v[j];
+          for (int j = 0; j < 32; ++j) part[BLOCK_M * PITCH + c * 32 + j] = n_ones ? v[j] : 0.f;  // no share: the accumulator was never written
         }
       }
     }
@@ -215,7 +224,7 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
   cluster_sync_all();  // every CTA's partial is in its shared memory
   const uint32_t part_addr = tiles;  // same offset in every CTA of the cluster
   constexpr int q4 = BN / 4;
-  if (!is_db) {
+  {
     const int rows_per_cta = (BLOCK_M + S - 1) / S;  // any cluster size: the last CTAs take the remainder
     for (int idx = threadIdx.x; idx < rows_per_cta * q4; idx += NUM_THREADS) {
       const int r = (int)rank * rows_per_cta + idx / q4, c4 = idx % q4;
@@ -230,17 +239,13 @@ umma_dw_cluster_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_c
       }
       *reinterpret_cast<float4*>(dst) = s;
     }
-  } else if (rank == 0) {
+  }
+  if (rank == 0) {  // this cluster's bias-gradient partial (its share of the k-blocks, all splits)
     for (int c4 = threadIdx.x; c4 < q4; c4 += NUM_THREADS) {
       const int col = n_blk * BN + c4 * 4;
       if (col >= p.N) continue;
-      float4 s = cluster_sum4(part_addr + (uint32_t)(c4 * 4) * 4u, S);
-      float* dst = p.b + col;
-      if (p.apply) {
-        const float4 b = *reinterpret_cast<const float4*>(dst);
-        s = make_float4(b.x - p.lr * s.x, b.y - p.lr * s.y, b.z - p.lr * s.z, b.w - p.lr * s.w);
-      }
-      *reinterpret_cast<float4*>(dst) = s;
+      const float4 s = cluster_sum4(part_addr + (uint32_t)(BLOCK_M * PITCH + c4 * 4) * 4u, S);
+      *reinterpret_cast<float4*>(p.db_part + (int64_t)m_blk * p.db_np + col) = s;
     }
   }
   cluster_sync_all();  // nobody leaves while a neighbour still reads its shared memory
@@ -254,7 +259,7 @@ std::atomic<int> g_cluster_dw_bf16{1};
 
 template <int BN>
 int plan_splits(int64_t B, int64_t K, int64_t N) {
-  const long clusters = ((long)cdiv(K, BLOCK_M) + 1) * cdiv(N, BN);  // tiles + one bias cluster per column block
+  const long clusters = (long)cdiv(K, BLOCK_M) * cdiv(N, BN);  // one cluster per output tile
   const long num_kb = cdiv(B, BLOCK_K);
   const int sms = umma_num_sms() - umma_sm_reserve();
   auto kern = umma_dw_cluster_kernel<BN>;
@@ -294,7 +299,7 @@ template <int BN>
 int launch(const CUtensorMap& ta, const CUtensorMap& tb, const DwClParams& p, cudaStream_t st) {
   auto kern = umma_dw_cluster_kernel<BN>;
   cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)((p.m_blocks + 1) * p.n_blocks * p.splits));
+  cfg.gridDim = dim3((unsigned)(p.m_blocks * p.n_blocks * p.splits));
   cfg.blockDim = dim3(NUM_THREADS);
   cfg.dynamicSmemBytes = ClCfg<BN>::SMEM_BYTES;
   cfg.stream = st;
@@ -318,12 +323,13 @@ void umma_set_cluster_dw(int on) { g_cluster_dw_bf16.store(on ? 1 : 0); }
 
 // *taken = 0: no cluster plan for this shape (or switched off): the caller runs the workspace path.
 int umma_dw_cluster(const bf16* X, const bf16* dZ, float* W_master, bf16* W_shadow, float* bias, float* dW_out,
-                    float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N, int* taken, cudaStream_t st) {
+                    float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N, float* db_part, int* taken,
+                    cudaStream_t st) {
   *taken = 0;
   if (!g_cluster_dw_bf16.load()) return DDNN_OK;
   float* w = apply ? W_master : dW_out;
   float* b = apply ? bias : db_out;
-  if (!w || !b || (reinterpret_cast<uintptr_t>(w) & 15u) || (reinterpret_cast<uintptr_t>(b) & 15u) ||
+  if (!w || !b || !db_part || (reinterpret_cast<uintptr_t>(w) & 15u) || (reinterpret_cast<uintptr_t>(db_part) & 15u) ||
       (apply && W_shadow && (reinterpret_cast<uintptr_t>(W_shadow) & 7u)))
     return DDNN_OK;
   const int bn = N >= 192 ? 256 : (N >= 96 ? 128 : 64);
@@ -354,18 +360,20 @@ int umma_dw_cluster(const bf16* X, const bf16* dZ, float* W_master, bf16* W_shad
   p.splits = S;
   p.w = w;
   p.shadow = apply ? W_shadow : nullptr;
-  p.b = b;
   p.lr = lr;
   p.apply = apply ? 1 : 0;
+  p.db_part = db_part;
+  p.db_np = (int)((N + 3) & ~(int64_t)3);
   CUtensorMap ta, tb;
   int rc = umma_get_tmap(X, 2, (uint64_t)K, (uint64_t)B, 64, 64, 0, &ta);  // MN-major: stored [B][K], box {64 K, 64 rows}
   if (rc != DDNN_OK) return rc;
   rc = umma_get_tmap(dZ, 2, (uint64_t)N, (uint64_t)B, 64, 64, 0, &tb);
   if (rc != DDNN_OK) return rc;
   *taken = 1;
-  if (bn == 256) return launch<256>(ta, tb, p, st);
-  if (bn == 128) return launch<128>(ta, tb, p, st);
-  return launch<64>(ta, tb, p, st);
+  rc = bn == 256 ? launch<256>(ta, tb, p, st) : (bn == 128 ? launch<128>(ta, tb, p, st) : launch<64>(ta, tb, p, st));
+  if (rc != DDNN_OK) return rc;
+  // the m_blocks bias partials -> bias update / db store (a one-row reduction; launch and prologue overlap the GEMM)
+  return reduce_dw2(nullptr, db_part, 1, p.m_blocks, K, N, nullptr, nullptr, bias, nullptr, db_out, lr, apply, st);
 }
 
 }  // namespace ddnn
