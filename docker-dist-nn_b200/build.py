@@ -15,7 +15,7 @@ HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "libddnn.so"
 SOURCES = ["ddnn_api.cu", "ddnn_simt.cu", "ddnn_reduce.cu", "ddnn_softmax.cu", "ddnn_umma.cu",
-           "ddnn_noalloc.cu", "ddnn_skinny.cu", "ddnn_peer.cu", "ddnn_outlayer.cu", "ddnn_tf32.cu", "ddnn_tail2.cu", "ddnn_umma_dwcl.cu"]
+           "ddnn_noalloc.cu", "ddnn_skinny.cu", "ddnn_peer.cu", "ddnn_outlayer.cu", "ddnn_tf32.cu", "ddnn_tail2.cu"]
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 

@@ -130,7 +130,6 @@ int ddnn_set_f32_tensor_cores(int mode) {
 
 int ddnn_set_cluster_split_k(int on) {
   tf32_set_cluster_dw(on);
-  umma_set_cluster_dw(on);
   return DDNN_OK;
 }
 
@@ -360,12 +359,6 @@ int ddnn_dense_backward_dw_sgd(const void* X, const void* dZ, float* W_master, v
   }
   if (use_umma(dtype, B, K, N, {X, dZ, W_master, W_shadow, dW_out})) {
     const int splits = umma_dw_splits(B, K, N);
-    if (splits > 1) {  // split-K reduced inside the kernel across a thread-block cluster when a one-wave plan exists
-      int taken = 0;
-      rc = umma_dw_cluster((const bf16*)X, (const bf16*)dZ, W_master, (bf16*)W_shadow, bias, dW_out, db_out, lr, apply,
-                           B, K, N, ws, &taken, st);
-      if (rc || taken) return rc;
-    }
     float* dw_part = splits > 1 ? ws : nullptr;
     float* db_part = ws + (splits > 1 ? (size_t)splits * K * np : 0);
     int cs = colsum_splits(B, N), db_fused = 0;

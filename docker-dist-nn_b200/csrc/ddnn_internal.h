@@ -108,11 +108,5 @@ int tf32_dw_partials(const float* X, const float* dZ, float* dw_part, int splits
 int tf32_dw_cluster(const float* X, const float* dZ, float* W_master, float* bias, float* dW_out, float* db_out, float lr,
                     int apply, int64_t B, int64_t K, int64_t N, int* taken, cudaStream_t st);
 void tf32_set_cluster_dw(int on);
-// the same for bf16 operands (ddnn_umma_dwcl.cu): one cluster per output tile, the bias gradient spread over the
-// row-block clusters (partials in the workspace + a one-row reducer); updates W_master / W_shadow / bias or stores
-int umma_dw_cluster(const bf16* X, const bf16* dZ, float* W_master, bf16* W_shadow, float* bias, float* dW_out,
-                    float* db_out, float lr, int apply, int64_t B, int64_t K, int64_t N, float* db_part /* workspace:
-                    cdiv(K,128) x Np floats */, int* taken, cudaStream_t st);
-void umma_set_cluster_dw(int on);
 
 }  // namespace ddnn

@@ -242,7 +242,7 @@ int ddnn_set_cta_pairs(int on);
 #define DDNN_F32_TC_DEFAULT 2
 int ddnn_set_f32_tensor_cores(int mode);
 
-/* Split-K dW GEMMs on tcgen05 (fp32 and bf16): 1 (default) = when a one-wave plan exists, the split-K partial tiles are reduced inside
+/* fp32 dW GEMMs on tcgen05: 1 (default) = when a one-wave plan exists, the split-K partial tiles are reduced inside
  * the kernel across a thread-block cluster (distributed shared memory) and the same kernel applies SGD / stores the
  * gradients -- one launch, no partial sums in HBM; 0 = always partials in the workspace + reducer launch.  Test /
  * profiling switch, process-wide.  No reference counterpart. */

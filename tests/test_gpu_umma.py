@@ -219,36 +219,3 @@ def test_signals_folded_into_the_gemm(cuda_device, bkn):
         _lib.check(_lib.lib.ddnn_flag_write(flags.data_ptr() + 8, 5, torch.cuda.current_stream().cuda_stream))
         side.synchronize()
         assert torch.equal(late, plain) and int(flags[3]) == 9
-
-
-@pytest.mark.timeout(180)
-@pytest.mark.parametrize("shape", [(4096, 784, 256), (65536, 784, 256), (8192, 1000, 256), (5000, 904, 136)])
-def test_cluster_split_k_dw_bf16(cuda_device, shape):
-    """bf16 dW with the split-K reduction inside the kernel (one thread-block cluster per output tile, partial tiles
-    summed through distributed shared memory, the bias gradient spread over the row-block clusters, SGD + bf16 shadow
-    written by the same kernel; shapes without a one-wave plan -- the last two -- take the workspace path): against the oracle on the bf16-rounded operands, against the workspace + reducer path
-    (summation order of the partials only) and bit-identical from run to run; ragged row / column / batch tails."""
-    from ddnn_b200 import _lib, ops
-    b, k, n = shape
-    g = torch.Generator(device="cuda").manual_seed(50)
-    x = torch.rand((b, k), device="cuda", generator=g).to(torch.bfloat16)
-    dz = (torch.randn((b, n), device="cuda", generator=g) / b).to(torch.bfloat16)
-    dw, db = ops.dense_backward_dw(x, dz)
-    dw2, db2 = ops.dense_backward_dw(x, dz)
-    assert torch.equal(dw, dw2) and torch.equal(db, db2)
-    ref_dw = to_np(x).T @ to_np(dz)
-    ref_db = to_np(dz).sum(axis=0)
-    assert rel_err(to_np(dw), ref_dw) < ACC_TOL and rel_err(to_np(db), ref_db) < ACC_TOL
-    w0 = torch.randn((k, n), device="cuda", generator=g) * 0.05
-    wm, bm = w0.clone(), torch.full((n,), 0.01, device="cuda")
-    sh = torch.zeros((k, n), dtype=torch.bfloat16, device="cuda")
-    ops.dense_backward_dw_sgd(x, dz, wm, bm, 0.5, w_shadow=sh)
-    assert rel_err(to_np(wm), to_np(w0) - 0.5 * ref_dw) < 1e-5
-    assert rel_err(to_np(bm), 0.01 - 0.5 * ref_db) < 1e-5
-    assert torch.equal(sh, wm.to(torch.bfloat16))
-    _lib.check(_lib.lib.ddnn_set_cluster_split_k(0))
-    try:
-        dw_ws, db_ws = ops.dense_backward_dw(x, dz)
-    finally:
-        _lib.check(_lib.lib.ddnn_set_cluster_split_k(1))
-    assert rel_err(to_np(dw), to_np(dw_ws)) < 2e-6 and rel_err(to_np(db), to_np(db_ws)) < 2e-6
