@@ -130,6 +130,7 @@ class Layer:
         self._bufs = None
         self._ws = None
         self._ws_cache: Dict[int, Any] = {}
+        self._chunk_ws_cache: Dict[int, int] = {}
         self._a0_ext: Optional[torch.Tensor] = None  # caller's batch read in place as layer 1's operand
         self._gen = 0  # bumped whenever the batch buffers are reallocated (captured graphs go stale)
         self._probe = None  # bench.py: list collecting (name, start_event, end_event) per entry-point call
@@ -414,6 +415,14 @@ class Layer:
             b["gw"] = [torch.empty_like(p["weights"]) for p in self.layer_params]
             b["gb"] = [torch.empty_like(p["biases"]) for p in self.layer_params]
         sl = slice(row0, row1)
+        need = self._chunk_ws_cache.get(row1 - row0)
+        if need is None:  # a chunk's split plan can need more scratch than the full batch's (plans are not monotone)
+            need = max(ops.dw_workspace_bytes(row1 - row0, p["weights"].shape[0], p["weights"].shape[1], self._cdt)
+                       for p in self.layer_params)
+            self._chunk_ws_cache[row1 - row0] = need
+        if need > self._ws.numel():
+            self._ws = torch.empty((need,), dtype=torch.uint8, device=self.device)
+            self._gen += 1
         for i, p in enumerate(self.layer_params):
             k_, n_ = p["weights"].shape
             with self._span(f"dW chunk L{i + 1} {k_}x{n_}"):
