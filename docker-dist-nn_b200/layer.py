@@ -131,6 +131,7 @@ class Layer:
         self._ws = None
         self._ws_cache: Dict[int, Any] = {}
         self._chunk_ws_cache: Dict[int, int] = {}
+        self._ws_chunk: Optional[torch.Tensor] = None
         self._a0_ext: Optional[torch.Tensor] = None  # caller's batch read in place as layer 1's operand
         self._gen = 0  # bumped whenever the batch buffers are reallocated (captured graphs go stale)
         self._probe = None  # bench.py: list collecting (name, start_event, end_event) per entry-point call
@@ -420,14 +421,16 @@ class Layer:
             need = max(ops.dw_workspace_bytes(row1 - row0, p["weights"].shape[0], p["weights"].shape[1], self._cdt)
                        for p in self.layer_params)
             self._chunk_ws_cache[row1 - row0] = need
-        if need > self._ws.numel():
-            self._ws = torch.empty((need,), dtype=torch.uint8, device=self.device)
-            self._gen += 1
+        ws = self._ws
+        if need > ws.numel():  # own buffer: the batch buffers (and what peers / captured graphs hold of them) stay put
+            if self._ws_chunk is None or self._ws_chunk.numel() < need:
+                self._ws_chunk = torch.empty((need,), dtype=torch.uint8, device=self.device)
+            ws = self._ws_chunk
         for i, p in enumerate(self.layer_params):
             k_, n_ = p["weights"].shape
             with self._span(f"dW chunk L{i + 1} {k_}x{n_}"):
                 ops.dense_backward_dw_accumulate(self._a(i)[sl], b["dz"][i][sl], b["gw"][i], b["gb"][i], first,
-                                                 workspace=self._ws)
+                                                 workspace=ws)
 
     def apply_update(self, lr: float) -> None:
         """W -= lr * dW, b -= lr * db from the accumulators of ``accumulate_grads``; bf16 shadow refreshed."""
