@@ -176,8 +176,9 @@ __global__ void __launch_bounds__(NUM_THREADS, 1)
 tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  const Tf32Params p, const Epi epi) {
   using C = TCfg<BN>;
-  static_assert(!CL || (A_MN && B_MN), "cluster split-K is the dW layout");
-  constexpr int NACC = (A_MN && B_MN) ? 1 : C::NACC_FWD;  // accumulator sets per tile (see TCfg)
+  constexpr bool DW = A_MN && B_MN;
+  // accumulator sets per tile (see TCfg); split-K tiles (dW, cluster split-K) have short chains and use one
+  constexpr int NACC = (DW || CL) ? 1 : C::NACC_FWD;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   const uint32_t tiles = (raw + 1023u) & ~1023u;
@@ -386,7 +387,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
                 make_float4(v[4 * j] + w[4 * j], v[4 * j + 1] + w[4 * j + 1], v[4 * j + 2] + w[4 * j + 2],
                             v[4 * j + 3] + w[4 * j + 3]);
         }
-        if (t.m_blk == 0 && q == 0) {  // bias-gradient partial: TMEM lane 0 of the ones-accumulators
+        if (DW && t.m_blk == 0 && q == 0) {  // bias-gradient partial: TMEM lane 0 of the ones-accumulators
           float* dbp = part + BLOCK_M * PITCH;
 #pragma unroll 1
           for (int c = 0; c < BN / 32; ++c) {
@@ -456,6 +457,10 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
         for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
       }
+      if (!DW) {  // forward / dX: the layout's own epilogue (bias + activation, activation derivative) on the sum
+        epi.apply4((int64_t)row, col, s, 4, true);
+        continue;
+      }
       float* dst = p.cl_w + (int64_t)row * p.N + col;
       if (p.cl_apply) {
         float4 w = *reinterpret_cast<const float4*>(dst);
@@ -464,7 +469,7 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       }
       *reinterpret_cast<float4*>(dst) = s;
     }
-    if (t.m_blk == 0 && cl_rank == 0) {  // bias gradient of this column block
+    if (DW && t.m_blk == 0 && cl_rank == 0) {  // bias gradient of this column block
       for (int c4 = threadIdx.x; c4 < q4; c4 += NUM_THREADS) {
         const int col = t.n_blk * BN + c4 * 4;
         if (col >= p.N) continue;
@@ -549,20 +554,19 @@ int launch_bn(int bn, const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Pa
   return launch_one<A_MN, B_MN, 32, Epi>(ta, tb, p, epi, st);
 }
 
-// Cluster split-K plan of the dW GEMM: S CTAs per output tile, S in {16, 8, 4, 2} (S divides the 128 tile rows).
-// Wanted: one wave (tiles * S <= SMs), >= 2 k-blocks per split, accumulation chains within DDNN_TF32_MAX_CHAIN
-// (S >= B / 2048), 16-byte aligned outputs.  Returns 0 when no S fits (the workspace path takes the layer).
-template <int BN>
-int cluster_splits_for(int64_t B, int64_t K, int64_t N, int* max_clusters_out) {
-  const long tiles = (long)cdiv(K, BLOCK_M) * cdiv(N, BN);
-  const long num_kb = cdiv(B, BLOCK_K);
-  const long min_by_chain = cdiv(B, DDNN_TF32_MAX_CHAIN);
-  auto kern = tf32_gemm_kernel<true, true, BN, EpiStoreF32, true>;
+// Cluster split-K plan: S CTAs per output tile, S in {16, 8, 4, 2} (S divides the 128 tile rows).  Wanted: one wave
+// (tiles * S <= SMs) that uses at least `min_ctas` SMs, >= 2 k-blocks per split, S >= `min_s` (accumulation chains
+// within DDNN_TF32_MAX_CHAIN), all clusters co-resident (a B200 holds 7 clusters of more than 8 CTAs).  Returns 0
+// when no S fits (the caller keeps its other plan).
+template <bool A_MN, bool B_MN, int BN, typename Epi>
+int cluster_plan(long tiles, long num_kb, long min_s, long min_ctas) {
+  auto kern = tf32_gemm_kernel<A_MN, B_MN, BN, Epi, true>;
   if (ensure_dynamic_smem((const void*)kern, TCfg<BN>::SMEM_BYTES) != DDNN_OK) return 0;
   static const int dbg_max_s = getenv("DDNN_DBG_CLUSTER_S") ? atoi(getenv("DDNN_DBG_CLUSTER_S")) : 16;  // measurement knob
   for (int S : {16, 8, 4, 2}) {
     if (S > dbg_max_s) continue;
-    if (tiles * S > ctas_available() || num_kb / S < 2 || S < min_by_chain) continue;
+    if (tiles * S > ctas_available() || tiles * S < min_ctas || num_kb / S < 2 || S < min_s) continue;
+    if (cdiv(num_kb, cdiv(num_kb, S)) != S) continue;  // the k-blocks do not split S ways
     if (S > 8 && cudaFuncSetAttribute((const void*)kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
       cudaGetLastError();
       continue;
@@ -583,17 +587,14 @@ int cluster_splits_for(int64_t B, int64_t K, int64_t N, int* max_clusters_out) {
       cudaGetLastError();
       continue;
     }
-    if (max_clusters >= tiles) {  // all clusters co-resident: one wave
-      if (max_clusters_out) *max_clusters_out = max_clusters;
-      return S;
-    }
+    if (max_clusters >= tiles) return S;  // all clusters co-resident: one wave
   }
   return 0;
 }
 
-template <int BN>
-int launch_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Params& p, cudaStream_t st) {
-  auto kern = tf32_gemm_kernel<true, true, BN, EpiStoreF32, true>;
+template <bool A_MN, bool B_MN, int BN, typename Epi>
+int launch_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Params& p, const Epi& epi, cudaStream_t st) {
+  auto kern = tf32_gemm_kernel<A_MN, B_MN, BN, Epi, true>;
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3((unsigned)(p.m_blocks * p.n_blocks * p.splits));
   cfg.blockDim = dim3(NUM_THREADS);
@@ -608,10 +609,62 @@ int launch_cluster(const CUtensorMap& ta, const CUtensorMap& tb, const Tf32Param
   attr[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
   cfg.numAttrs = g_pdl.load(std::memory_order_relaxed) ? 2 : 1;
-  EpiStoreF32 unused{nullptr, 0};
-  DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, unused));
+  DDNN_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, ta, tb, p, epi));
   count_launch();
   return DDNN_OK;
+}
+
+// plan look-up once per (device, shape): the occupancy query is a driver call
+struct PlanCache {
+  std::mutex mu;
+  std::map<std::tuple<int, int64_t, int64_t, int64_t>, int> plans;
+  template <typename F>
+  int get(int64_t B, int64_t K, int64_t N, F&& compute) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const auto key = std::make_tuple(dev, B, K, N);
+    {
+      std::lock_guard<std::mutex> g(mu);
+      auto it = plans.find(key);
+      if (it != plans.end()) return it->second;
+    }
+    const int S = compute();
+    std::lock_guard<std::mutex> g(mu);
+    if (plans.size() > 4096) plans.clear();
+    plans[key] = S;
+    return S;
+  }
+};
+
+// Forward / dX with few output tiles and a long reduction (MNIST layer 1: 32 tiles of 128 x 128, 25 k-blocks): the
+// plain plan shrinks the tile width until ~every SM has a tile and walks all k-blocks serially in each CTA, which is
+// what the launch is bound by (25 x ~0.5 us).  With the widest tile and the reduction split over a cluster, each
+// CTA walks 1/S of the k-blocks; the partial tiles are summed through distributed shared memory and the layout's
+// epilogue (bias + activation / activation derivative) runs on the sum.  *taken = 0: no plan, run the plain kernel.
+template <bool A_MN, bool B_MN, typename Epi>
+int forward_like_cluster(PlanCache& cache, const float* A, const float* Bm, int64_t M, int64_t N, int64_t Kred,
+                         const Epi& epi, int* taken, cudaStream_t st) {
+  *taken = 0;
+  const int bn = N >= 128 ? 128 : (N >= 64 ? 64 : 32);
+  const long tiles = (long)cdiv(M, BLOCK_M) * cdiv(N, bn), num_kb = cdiv(Kred, BLOCK_K);
+  if (num_kb < 8 || tiles * 2 > ctas_available()) return DDNN_OK;
+  const long min_ctas = (long)ctas_available() * 3 / 5;
+  const int S = cache.get(M, Kred, N, [&] {
+    return bn == 128 ? cluster_plan<A_MN, B_MN, 128, Epi>(tiles, num_kb, 1, min_ctas)
+                     : (bn == 64 ? cluster_plan<A_MN, B_MN, 64, Epi>(tiles, num_kb, 1, min_ctas)
+                                 : cluster_plan<A_MN, B_MN, 32, Epi>(tiles, num_kb, 1, min_ctas));
+  });
+  if (S == 0) return DDNN_OK;
+  CUtensorMap ta, tb;
+  int rc = operand_maps(A_MN, A, B_MN, Bm, M, N, Kred, bn, &ta, &tb);
+  if (rc != DDNN_OK) return rc;
+  Tf32Params p{};
+  fill_tiles(p, M, N, Kred, bn, S);
+  if (p.splits != S) return DDNN_OK;
+  *taken = 1;
+  if (bn == 128) return launch_cluster<A_MN, B_MN, 128, Epi>(ta, tb, p, epi, st);
+  if (bn == 64) return launch_cluster<A_MN, B_MN, 64, Epi>(ta, tb, p, epi, st);
+  return launch_cluster<A_MN, B_MN, 32, Epi>(ta, tb, p, epi, st);
 }
 
 std::atomic<int> g_cluster_dw{1};
@@ -637,23 +690,14 @@ int tf32_dw_cluster(const float* X, const float* dZ, float* W_master, float* bia
                 BLOCK_M * (64 + CL_PITCH_PAD) * 4 + 64 * 4 <= TCfg<64>::STAGES * (int)TCfg<64>::STAGE_BYTES &&
                 BLOCK_M * (32 + CL_PITCH_PAD) * 4 + 32 * 4 <= TCfg<32>::STAGES * (int)TCfg<32>::STAGE_BYTES,
                 "the partial tile must fit in the operand ring it overlays");
-  // the plan needs an occupancy query: look it up once per (device, shape)
-  static std::mutex mu;
-  static std::map<std::tuple<int, int64_t, int64_t, int64_t>, int> plans;
-  int dev = 0, S = -1;
-  DDNN_CUDA_CHECK(cudaGetDevice(&dev));
-  {
-    std::lock_guard<std::mutex> g(mu);
-    auto it = plans.find(std::make_tuple(dev, B, K, N));
-    if (it != plans.end()) S = it->second;
-  }
-  if (S < 0) {
-    S = bn == 128 ? cluster_splits_for<128>(B, K, N, nullptr)
-                  : (bn == 64 ? cluster_splits_for<64>(B, K, N, nullptr) : cluster_splits_for<32>(B, K, N, nullptr));
-    std::lock_guard<std::mutex> g(mu);
-    if (plans.size() > 4096) plans.clear();
-    plans[std::make_tuple(dev, B, K, N)] = S;
-  }
+  static PlanCache cache;
+  const long tiles = (long)cdiv(K, BLOCK_M) * cdiv(N, bn), num_kb = cdiv(B, BLOCK_K);
+  const long min_s = cdiv(B, DDNN_TF32_MAX_CHAIN);
+  const int S = cache.get(B, K, N, [&] {
+    return bn == 128 ? cluster_plan<true, true, 128, EpiStoreF32>(tiles, num_kb, min_s, 0)
+                     : (bn == 64 ? cluster_plan<true, true, 64, EpiStoreF32>(tiles, num_kb, min_s, 0)
+                                 : cluster_plan<true, true, 32, EpiStoreF32>(tiles, num_kb, min_s, 0));
+  });
   if (S == 0) return DDNN_OK;
   CUtensorMap ta, tb;
   int rc = operand_maps(true, X, true, dZ, K, N, B, bn, &ta, &tb);
@@ -666,9 +710,10 @@ int tf32_dw_cluster(const float* X, const float* dZ, float* W_master, float* bia
   p.cl_lr = lr;
   p.cl_apply = apply ? 1 : 0;
   *taken = 1;
-  if (bn == 128) return launch_cluster<128>(ta, tb, p, st);
-  if (bn == 64) return launch_cluster<64>(ta, tb, p, st);
-  return launch_cluster<32>(ta, tb, p, st);
+  const EpiStoreF32 unused{nullptr, 0};
+  if (bn == 128) return launch_cluster<true, true, 128, EpiStoreF32>(ta, tb, p, unused, st);
+  if (bn == 64) return launch_cluster<true, true, 64, EpiStoreF32>(ta, tb, p, unused, st);
+  return launch_cluster<true, true, 32, EpiStoreF32>(ta, tb, p, unused, st);
 }
 
 // TMA needs 16-byte row pitches (widths % 4) and the boxes are 32 elements wide
@@ -686,6 +731,13 @@ int64_t tf32_max_reduction(int64_t M, int64_t N) {
 int tf32_forward(const float* X, const float* W, const float* bias, float* A, int64_t B, int64_t K, int64_t N, int act,
                  cudaStream_t st) {
   // D[B, N] = X[B, K] . W[K, N]: A operand K-major, B operand MN-major (W is [K][N] like grpc_node.py:51)
+  if (g_cluster_dw.load()) {
+    static PlanCache cache;
+    int taken = 0;
+    EpiFwd<float> epi{bias, A, N, act};
+    int rc = forward_like_cluster<false, true, EpiFwd<float>>(cache, X, W, B, N, K, epi, &taken, st);
+    if (rc || taken) return rc;
+  }
   const int bn = pick_bn(B, N);
   CUtensorMap ta, tb;
   int rc = operand_maps(false, X, true, W, B, N, K, bn, &ta, &tb);
@@ -699,6 +751,13 @@ int tf32_forward(const float* X, const float* W, const float* bias, float* A, in
 int tf32_dx(const float* dZ, const float* W, const float* Aprev, float* dZprev, int64_t B, int64_t K, int64_t N,
             int act_prev, cudaStream_t st) {
   // D[B, K] = dZ[B, N] . W[K, N]^T: both operands K-major (the reduction runs along W's rows)
+  if (g_cluster_dw.load()) {
+    static PlanCache cache;
+    int taken = 0;
+    EpiDx<float> epi{Aprev, dZprev, K, act_prev};
+    int rc = forward_like_cluster<false, false, EpiDx<float>>(cache, dZ, W, B, K, N, epi, &taken, st);
+    if (rc || taken) return rc;
+  }
   const int bn = pick_bn(B, K);
   CUtensorMap ta, tb;
   int rc = operand_maps(false, dZ, false, W, B, K, N, bn, &ta, &tb);

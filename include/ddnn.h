@@ -242,9 +242,11 @@ int ddnn_set_cta_pairs(int on);
 #define DDNN_F32_TC_DEFAULT 2
 int ddnn_set_f32_tensor_cores(int mode);
 
-/* fp32 dW GEMMs on tcgen05: 1 (default) = when a one-wave plan exists, the split-K partial tiles are reduced inside
- * the kernel across a thread-block cluster (distributed shared memory) and the same kernel applies SGD / stores the
- * gradients -- one launch, no partial sums in HBM; 0 = always partials in the workspace + reducer launch.  Test /
+/* fp32 GEMMs on tcgen05: 1 (default) = when a one-wave plan exists, the reduction is split over a thread-block
+ * cluster and the partial tiles are summed inside the kernel through distributed shared memory -- dW: the same kernel
+ * applies SGD / stores the gradients (one launch, no partial sums in HBM); forward / dX with few output tiles and a
+ * long reduction: each CTA walks 1 / S of the k-blocks, the epilogue runs on the sum.  0 = dW partials in the
+ * workspace + reducer launch, forward / dX un-split.  Test /
  * profiling switch, process-wide.  No reference counterpart. */
 int ddnn_set_cluster_split_k(int on);
 

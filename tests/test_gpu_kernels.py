@@ -419,3 +419,28 @@ def test_cluster_split_k_dw_f32(cuda_device, shape):
     finally:
         _lib.check(_lib.lib.ddnn_set_cluster_split_k(1))
     assert rel_err(to_np(dw), to_np(dw_ws)) < 2e-6 and rel_err(to_np(db), to_np(db_ws)) < 2e-6
+
+
+@pytest.mark.timeout(120)
+@pytest.mark.parametrize("shape", [(4096, 784, 128), (4096, 784, 256), (1000, 1024, 72), (2048, 2000, 512)])
+@pytest.mark.parametrize("act", ["relu", "sigmoid"])
+def test_cluster_split_k_forward_f32(cuda_device, shape, act):
+    """fp32 forward with few output tiles and a long reduction: the reduction is split over a thread-block cluster,
+    the partial tiles are summed through distributed shared memory and bias + activation run on the sum.  Against the
+    float64 oracle (normalised and per-element condition-sum bounds) and against the plain kernel (summation order
+    only); run-to-run bit-identical.  Shapes without a cluster plan simply take the plain kernel in both runs."""
+    from ddnn_b200 import _lib, ops
+    b, k, n = shape
+    x, w, bias = _data(b, k, n, seed=41)
+    xd, wd, bd = to_dev(x), to_dev(w), to_dev(bias)
+    ref = oracle.activate(np.dot(x, w) + bias, act)
+    got = ops.dense_forward(xd, wd, bd, act)
+    assert torch.equal(got, ops.dense_forward(xd, wd, bd, act))
+    assert rel_err(to_np(got), ref) < F32_TOL
+    assert cond_ok(to_np(got), ref, np.dot(np.abs(x), np.abs(w)) + np.abs(bias), F32_TOL)
+    _lib.check(_lib.lib.ddnn_set_cluster_split_k(0))
+    try:
+        plain = ops.dense_forward(xd, wd, bd, act)
+    finally:
+        _lib.check(_lib.lib.ddnn_set_cluster_split_k(1))
+    assert rel_err(to_np(got), to_np(plain)) < 2e-6
