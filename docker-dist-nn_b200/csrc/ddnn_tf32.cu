@@ -447,23 +447,24 @@ tf32_gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const int r = (int)cl_rank * rows_per_cta + idx / q4, c4 = idx % q4;
       const int row = t.m_blk * BLOCK_M + r, col = t.n_blk * BN + c4 * 4;
       if (row >= p.M || col >= p.N) continue;  // N % 4 == 0: a group of 4 columns is all in or all out
-      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int src = 0; src < S; src += 4) {  // 4 remote loads in flight, summed in a fixed order (deterministic)
-        float4 v[4];
+      // the weight this thread will update: its global load goes out first, under the remote loads
+      float* dst = DW ? p.cl_w + (int64_t)row * p.N + col : nullptr;
+      float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (DW && p.cl_apply) w = *reinterpret_cast<const float4*>(dst);
+      // all S <= 16 remote loads in flight at once, then summed in CTA order (deterministic)
+      float4 v[16];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-          v[u] = (src + u < S) ? ld_dsmem4(part_addr + (uint32_t)(r * PITCH + c4 * 4) * 4u, (uint32_t)(src + u))
-                               : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int u = 0; u < 16; ++u)
+        v[u] = (u < S) ? ld_dsmem4(part_addr + (uint32_t)(r * PITCH + c4 * 4) * 4u, (uint32_t)u)
+                       : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 s = v[0];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
-      }
+      for (int u = 1; u < 16; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
       if (!DW) {  // forward / dX: the layout's own epilogue (bias + activation, activation derivative) on the sum
         epi.apply4((int64_t)row, col, s, 4, true);
         continue;
       }
-      float* dst = p.cl_w + (int64_t)row * p.N + col;
       if (p.cl_apply) {
-        float4 w = *reinterpret_cast<const float4*>(dst);
         w.x -= p.cl_lr * s.x; w.y -= p.cl_lr * s.y; w.z -= p.cl_lr * s.z; w.w -= p.cl_lr * s.w;
         s = w;
       }
