@@ -474,3 +474,53 @@ def test_chunked_weight_gradient_and_update(cuda_device, dtype, dims, rows, chun
         assert np.array_equal(b["weights"], c["weights"]) and np.array_equal(b["biases"], c["biases"])
         assert rel_err(b["weights"], a["weights"]) < 1e-6 and rel_err(b["biases"], a["biases"]) < 1e-6
         assert rel_err(b["weights"], r["weights"]) < (F32_TOL if dtype == "f32" else BF16_ACT_TOL)
+
+
+def test_single_stage_pipeline_host_loop_and_relay(cuda_device):
+    """PipelineStage on ONE stage (what bench.py times at N = 1): `fit_stream` (pinned host batches, H2D per
+    micro-batch on a copy stream, the slot read in place) gives the same losses and weights as stepping on device
+    tensors, in both orders with equal gradient chunks; `infer` (forward-only relay on the resident buffers) equals
+    `process_matrix`."""
+    from ddnn_b200 import Layer
+    from ddnn_b200.pipeline import PipelineStage
+    dims, acts = [256, 256, 128, 64], ["relu", "sigmoid", "softmax"]
+    rows, micro = 1024, 8
+    batches = [synthetic_batch(rows, dims[0], dims[-1], seed=s) for s in range(3)]
+
+    def stage(schedule, dw_chunk):
+        L = Layer.from_params(make_params(dims, acts, seed=2), dims[0], dtype="bf16", is_output=True)
+        return PipelineStage(L, 0, 1, schedule=schedule, dw_chunk=dw_chunk)
+
+    dev_stage, host_stage, zb_stage = stage("gpipe", 2), stage("gpipe", 2), stage("zb", 2)
+    dev_losses = []
+    for x, y in batches:
+        xd = to_dev(x, torch.bfloat16)
+        dev_losses.append(dev_stage.train_step(xd, to_dev(y, torch.int32), rows, micro, 0.05).item())
+    host = [(torch.as_tensor(x, dtype=torch.float32).to(torch.bfloat16).pin_memory(),
+             torch.as_tensor(y, dtype=torch.int32).pin_memory()) for x, y in batches]
+    assert host_stage.fit_stream(host, rows, micro, 0.05) == dev_losses
+    assert zb_stage.fit_stream(host, rows, micro, 0.05) == dev_losses
+    for a, b, c in zip(dev_stage.layer.layer_params, host_stage.layer.layer_params, zb_stage.layer.layer_params):
+        assert torch.equal(a["weights"], b["weights"]) and torch.equal(a["weights"], c["weights"])
+        assert torch.equal(a["biases"], b["biases"]) and torch.equal(a["biases"], c["biases"])
+    xq = to_dev(batches[0][0], torch.bfloat16)
+    relay = dev_stage.infer(xq, rows, 3)
+    direct = dev_stage.layer.process_matrix(xq)
+    assert torch.equal(relay, direct)
+    ref = oracle.process_matrix(dev_stage.layer.export_params(), to_np(xq), dims[0])
+    assert rel_err(to_np(relay), ref) < BF16_ACT_TOL
+
+
+def test_fit_stream_takes_host_rows_in_the_compute_dtype(cuda_device):
+    """A bf16 model fed bf16 host rows (half the PCIe bytes, slot read in place) and fed the same values as fp32 rows
+    (cast on the device) trains to the same bits."""
+    from ddnn_b200 import Trainer
+    dims, acts = [784, 256, 256, 10], ["relu", "relu", "softmax"]
+    data = [synthetic_batch(512, 784, 10, seed=s) for s in range(4)]
+    hb = [(torch.as_tensor(x, dtype=torch.float32).to(torch.bfloat16).pin_memory(),
+           torch.as_tensor(y, dtype=torch.int32).pin_memory()) for x, y in data]
+    hf = [(xb.float().pin_memory(), yb) for xb, yb in hb]   # the same (bf16-representable) values as fp32
+    ta, tb = (Trainer(make_params(dims, acts, seed=1), dtype="bf16") for _ in range(2))
+    assert ta.fit_stream(hb, lr=0.05) == tb.fit_stream(hf, lr=0.05)
+    for a, b in zip(ta.export_params(), tb.export_params()):
+        assert np.array_equal(a["weights"], b["weights"])
