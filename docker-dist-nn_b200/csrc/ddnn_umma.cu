@@ -740,6 +740,12 @@ int launch_pair_ew(const CUtensorMap& ta, const CUtensorMap& tb, UmmaParams p, c
   constexpr uint64_t kEvictNormal = 0x1000000000000000ull;
   p.hint_a = kEvictNormal;
   p.hint_b = kEvictNormal;
+  {  // measurement knobs: DDNN_DBG_HINT_A / _B = 1 (evict_first) or 2 (evict_last)
+    static const int ha = dbg_env("DDNN_DBG_HINT_A"), hb = dbg_env("DDNN_DBG_HINT_B");
+    constexpr uint64_t kFirst = 0x12F0000000000000ull, kLast = 0x14F0000000000000ull;
+    if (ha) p.hint_a = ha == 1 ? kFirst : kLast;
+    if (hb) p.hint_b = hb == 1 ? kFirst : kLast;
+  }
   // tile space in 256-row blocks; rasterisation group halves accordingly
   p.m_blocks = cdiv(p.M, 256);
   p.group_m = p.group_m > 1 ? (p.group_m + 1) / 2 : 1;
