@@ -285,7 +285,9 @@ int ddnn_flag_wait(const int32_t* flag, int32_t value, void* stream);
  *              of ONE stream (each GEMM leaves it at zero); required when done_flag is given.
  * On shapes / dtypes that do not run on the tcgen05 kernels the same effect is produced with ddnn_flag_wait, the
  * plain kernel and ddnn_flag_write.  sig == NULL makes them identical to the plain entry points.  The polling
- * kernel occupies the GPU until the flag arrives: the producer must not depend on later work of this stream.
+ * kernel occupies the GPU until the flag arrives: the producer must not depend on later work of this stream, and
+ * a producer on ANOTHER STREAM OF THE SAME GPU must use kernels that are already loaded (the first launch of a
+ * kernel loads its module lazily, which can wait for the device to go idle).
  */
 typedef struct ddnn_signals {
   const int32_t* wait_flag;

@@ -208,6 +208,10 @@ def test_signals_folded_into_the_gemm(cuda_device, bkn):
     assert torch.equal(got_dx, plain_dx)
     # a wait that is satisfied only later, from another stream
     if b * n <= 512 * 256:  # few CTAs: the flag kernel of the other stream always finds a free SM
+        # the flag kernel must already be loaded: the first launch of a kernel loads its module lazily, and that can
+        # wait for the device to go idle -- which it never does while the GEMM below polls for this very flag
+        scratch_flag = torch.zeros((1,), dtype=torch.int32, device="cuda")
+        _lib.check(_lib.lib.ddnn_flag_write(scratch_flag.data_ptr(), 1, torch.cuda.current_stream().cuda_stream))
         torch.cuda.synchronize()
         side = torch.cuda.Stream()
         sig = ops.make_signals(flags.data_ptr() + 8, 5, flags.data_ptr() + 12, 9, counter.data_ptr())
