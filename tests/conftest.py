@@ -15,6 +15,15 @@ def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (B200); run with -m gpu")
 
 
+def pytest_collection_modifyitems(config, items):
+    """Every GPU test gets a 5-minute limit enforced from a watchdog thread: a kernel that never finishes blocks the
+    main thread inside the CUDA runtime, where a signal-based timeout cannot fire, and would hold the GPU box until
+    the outer limit."""
+    for item in items:
+        if item.get_closest_marker("gpu") is not None:
+            item.add_marker(pytest.mark.timeout(300, method="thread"))
+
+
 @pytest.fixture(scope="session")
 def golden_small():
     with open(os.path.join(GOLDEN, "golden_small.json")) as f:
